@@ -1,0 +1,411 @@
+// conv_tc.cu -- K3: every Conv2D(+BN+bias+ReLU+residual) of modelObj.predict
+// (/root/reference/models.py:40, :65) with Cin >= 16 as an implicit GEMM on the
+// 5th-gen tensor cores: D[pixels, cout] = im2col(A)[pixels, taps*cin] * W^T.
+//
+//   A tile : 128 output pixels x 64 channels of one filter tap, fetched by ONE
+//            im2col-mode TMA (cp.async.bulk.tensor.4d...im2col) with hardware
+//            zero fill for 'same' padding and element strides for stride 2.
+//   B tile : bn output channels x 64 of the packed bf16 weights, tiled TMA.
+//   MMA    : tcgen05.mma.cta_group::1.kind::f16, M=128, N=bn, K=16, bf16 in,
+//            fp32 accumulators in TMEM.
+//   Epilogue: tcgen05.ld -> +folded bias (+residual) -> ReLU -> bf16 -> strided
+//            NHWC store (channel slice of a concat buffer when pitch > cout).
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM alloc + MMA
+// issue, warps 2..5 = epilogue (TMEM lane quarter = warp_id % 4).
+#include "conv_tc.h"
+
+#include <cuda_bf16.h>
+#include <cudaTypedefs.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <string>
+
+namespace dml {
+namespace {
+
+thread_local std::string g_tc_err;
+int tc_fail(const char* fmt, ...) {
+  char buf[768];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_tc_err = buf;
+  return -1;
+}
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;                       // bf16 elements = one 128-byte swizzle row
+constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
+constexpr int TC_THREADS = 192;
+constexpr int SMEM_LIMIT = 227 * 1024;
+
+struct TcKernelParams {
+  const float* bias;
+  const __nv_bfloat16* res;
+  __nv_bfloat16* out;
+  int M;         // valid output pixels (n * ho * wo)
+  int ho, wo;
+  int stride, pad_h, pad_w;
+  int kw, num_kb, cpb;
+  int bn, out_pitch, res_pitch, relu;
+  int stages, tmem_cols;
+};
+
+// ------------------------------- PTX helpers -------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// Bounded wait: a protocol bug traps (kernel error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  long long t0 = clock64();
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    if (clock64() - t0 > 4000000000LL) __trap();
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int x, int y) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(x), "r"(y)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c, int w, int h,
+                                                   int n, uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accum)
+      : "memory");
+}
+// K-major, 128-byte swizzle: rows 128 B apart, 8-row groups 1024 B apart (SBO),
+// LBO unused (1), descriptor version 1 (sm_100), layout type 2 (SWIZZLE_128B).
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// ------------------------------- the kernel --------------------------------
+__global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_constant__ CUtensorMap map_a,
+                                                             const __grid_constant__ CUtensorMap map_b,
+                                                             const TcKernelParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B tiles need 1024-B alignment
+  const int stages = p.stages;
+  const uint32_t b_stage_bytes = (uint32_t)p.bn * 128u;
+  const uint32_t sA = base;
+  const uint32_t sB = sA + (uint32_t)stages * A_STAGE_BYTES;
+  const uint32_t bars = sB + (uint32_t)stages * b_stage_bytes;
+  const uint32_t full0 = bars, empty0 = bars + 8u * stages, tmem_full = bars + 16u * stages;
+  const uint32_t tmem_slot = tmem_full + 8u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BLOCK_M;
+  const int n0 = blockIdx.y * p.bn;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    for (int i = 0; i < stages; ++i) {
+      mbar_init(full0 + 8u * i, 1);
+      mbar_init(empty0 + 8u * i, 1);
+    }
+    mbar_init(tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(p.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---- TMA producer: one (tap, 64-channel block) per pipeline stage ----
+      const int howo = p.ho * p.wo;
+      const int img = m0 / howo;
+      const int rem = m0 - img * howo;
+      const int oh = rem / p.wo, ow = rem - oh * p.wo;
+      const int w_base = ow * p.stride - p.pad_w;  // im2col base pixel = top-left of the filter window
+      const int h_base = oh * p.stride - p.pad_h;
+      const uint32_t tx_bytes = A_STAGE_BYTES + b_stage_bytes;
+      for (int j = 0; j < p.num_kb; ++j) {
+        const int s = j % stages;
+        const uint32_t ph = (uint32_t)(j / stages) & 1u;
+        mbar_wait(empty0 + 8u * s, ph ^ 1u);
+        mbar_arrive_expect_tx(full0 + 8u * s, tx_bytes);
+        const int tap = j / p.cpb, cb = j - tap * p.cpb;
+        const int r = tap / p.kw, sx = tap - r * p.kw;
+        tma_load_im2col_4d(sA + (uint32_t)s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base, img,
+                           (uint16_t)sx, (uint16_t)r);
+        tma_load_2d(sB + (uint32_t)s * b_stage_bytes, &map_b, full0 + 8u * s, j * BLOCK_K, n0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ---- MMA issuer ----
+      // idesc: D=f32 (bit 4), A=bf16 (bit 7), B=bf16 (bit 10), K-major A and B,
+      //        N>>3 at bit 17, M>>4 at bit 24.
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+      for (int j = 0; j < p.num_kb; ++j) {
+        const int s = j % stages;
+        const uint32_t ph = (uint32_t)(j / stages) & 1u;
+        mbar_wait(full0 + 8u * s, ph);
+        tc_fence_after();
+        const uint64_t da = make_sw128_desc(sA + (uint32_t)s * A_STAGE_BYTES);
+        const uint64_t db = make_sw128_desc(sB + (uint32_t)s * b_stage_bytes);
+#pragma unroll
+        for (int k = 0; k < BLOCK_K / 16; ++k) {
+          // advancing K by 16 bf16 = 32 bytes inside the swizzle row: +2 in the (addr >> 4) field
+          umma_bf16(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((j | k) != 0));
+        }
+        umma_commit(empty0 + 8u * s);  // frees the smem stage when these MMAs retire
+      }
+      umma_commit(tmem_full);  // accumulator complete
+    }
+  } else {
+    // ---- epilogue: warp q owns TMEM lanes [32q, 32q+32) = tile rows ----
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const long long m = (long long)m0 + row;
+    const bool row_ok = m < p.M;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    __nv_bfloat16* orow = p.out + m * p.out_pitch + n0;
+    const __nv_bfloat16* rrow = p.res ? p.res + m * p.res_pitch + n0 : nullptr;
+    for (int c0 = 0; c0 < p.bn; c0 += 16) {
+      uint32_t v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+      if (row_ok) {
+        float f[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]) + __ldg(p.bias + n0 + c0 + i);
+        if (rrow) {
+          uint4 r0 = *reinterpret_cast<const uint4*>(rrow + c0);
+          uint4 r1 = *reinterpret_cast<const uint4*>(rrow + c0 + 8);
+          const __nv_bfloat16* rb0 = reinterpret_cast<const __nv_bfloat16*>(&r0);
+          const __nv_bfloat16* rb1 = reinterpret_cast<const __nv_bfloat16*>(&r1);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            f[i] += __bfloat162float(rb0[i]);
+            f[8 + i] += __bfloat162float(rb1[i]);
+          }
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
+        }
+        __align__(16) __nv_bfloat16 o[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) o[i] = __float2bfloat16_rn(f[i]);
+        *reinterpret_cast<uint4*>(orow + c0) = *reinterpret_cast<const uint4*>(o);
+        *reinterpret_cast<uint4*>(orow + c0 + 8) = *reinterpret_cast<const uint4*>(o + 8);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+  }
+}
+
+}  // namespace
+
+// ------------------------------- host side ---------------------------------
+namespace {
+
+PFN_cuTensorMapEncodeTiled g_encode_tiled = nullptr;
+PFN_cuTensorMapEncodeIm2col g_encode_im2col = nullptr;
+int g_driver_version = 0;
+
+int pick_bn(int cout, int override_bn) {
+  if (override_bn > 0) return (cout % override_bn == 0 && override_bn % 16 == 0 && override_bn <= 256) ? override_bn : 0;
+  if (cout <= 128) return cout;
+  for (int bn = 128; bn >= 16; bn -= 16)
+    if (cout % bn == 0) return bn;
+  return 0;
+}
+
+}  // namespace
+
+const char* tc_last_error() { return g_tc_err.c_str(); }
+
+bool tc_supported(const Op& op) {
+  return op.kind == OP_CONV && op.cin >= 16 && op.cin % 8 == 0 && op.cout % 16 == 0 && op.cin_pad % BLOCK_K == 0 &&
+         pick_bn(op.cout, 0) > 0;
+}
+
+int tc_init() {
+  if (!g_encode_tiled) {
+    cudaDriverEntryPointQueryResult qres;
+    void* fn = nullptr;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
+      return tc_fail("cuTensorMapEncodeTiled not available from the driver (%s)", cudaGetErrorString(e));
+    g_encode_tiled = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(fn);
+    fn = nullptr;
+    e = cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
+      return tc_fail("cuTensorMapEncodeIm2col not available from the driver (%s)", cudaGetErrorString(e));
+    g_encode_im2col = reinterpret_cast<PFN_cuTensorMapEncodeIm2col>(fn);
+    cudaDriverGetVersion(&g_driver_version);
+  }
+  cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
+  return 0;
+}
+
+size_t tc_scratch_bytes(const Net&, int) { return 0; }
+
+int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune& tune) {
+  if (!g_encode_tiled) return tc_fail("tc_init was not called");
+  TcOpPlan op;
+  op.bn = pick_bn(p.cout, tune.bn);
+  if (op.bn == 0) return tc_fail("no N tile for cout = %d (override %d)", p.cout, tune.bn);
+  if (p.cin_pad % BLOCK_K) return tc_fail("cin_pad = %d is not a multiple of %d", p.cin_pad, BLOCK_K);
+  op.cpb = p.cin_pad / BLOCK_K;
+  const int num_kb = p.kh * p.kw * op.cpb;
+  const int stage_bytes = A_STAGE_BYTES + op.bn * 128;
+  int target = op.bn <= 64 ? 3 : (op.bn <= 128 ? 3 : 4);
+  if (tune.stages > 0) target = tune.stages;
+  if (target > num_kb) target = num_kb;
+  while (target > 1 && target * stage_bytes + 2048 > SMEM_LIMIT) --target;
+  op.stages = target;
+  op.smem = (size_t)op.stages * stage_bytes + 1024 /*alignment slack*/ + 16 * op.stages + 64;
+  op.tmem_cols = 32;
+  while (op.tmem_cols < op.bn) op.tmem_cols *= 2;
+
+  // A: NHWC view as (C, W, H, N), im2col mode.  Corner convention as in CUTLASS'
+  // make_im2col_tma_copy_desc: lower = -pad, upper = pad - (filter - 1); index 0 = W.
+  cuuint64_t gdim[4] = {(cuuint64_t)p.cin, (cuuint64_t)p.wi, (cuuint64_t)p.hi, (cuuint64_t)n_capacity};
+  cuuint64_t gstr[3] = {(cuuint64_t)p.in_pitch * 2, (cuuint64_t)p.wi * p.in_pitch * 2,
+                        (cuuint64_t)p.hi * p.wi * p.in_pitch * 2};
+  int lower[2] = {-p.pad_w, -p.pad_h};
+  int upper[2] = {p.pad_w - (p.kw - 1), p.pad_h - (p.kh - 1)};
+  cuuint32_t estr[4] = {1, (cuuint32_t)p.stride, (cuuint32_t)p.stride, 1};
+  CUresult r = g_encode_im2col(&op.map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p.in), gdim, gstr, lower,
+                               upper, BLOCK_K, BLOCK_M, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return tc_fail("cuTensorMapEncodeIm2col failed (%d): C=%d W=%d H=%d N=%d pitch=%d k=%dx%d s=%d pad=%d,%d", (int)r, p.cin,
+                   p.wi, p.hi, n_capacity, p.in_pitch, p.kh, p.kw, p.stride, p.pad_h, p.pad_w);
+  // Same small-tensor fix-up CUTLASS applies for drivers <= 13.1 (tensors < 128 KiB).
+  if (g_driver_version <= 13010 && (size_t)n_capacity * p.hi * p.wi * p.in_pitch * 2 < 131072)
+    reinterpret_cast<uint64_t*>(&op.map_a)[1] &= ~(1ull << 21);
+
+  // B: packed weights [cout][taps*cin_pad], K contiguous.
+  const cuuint64_t ktot = (cuuint64_t)p.kh * p.kw * p.cin_pad;
+  cuuint64_t bdim[2] = {ktot, (cuuint64_t)p.cout};
+  cuuint64_t bstr[1] = {ktot * 2};
+  cuuint32_t bbox[2] = {BLOCK_K, (cuuint32_t)op.bn};
+  cuuint32_t bes[2] = {1, 1};
+  r = g_encode_tiled(&op.map_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(p.w), bdim, bstr, bbox, bes,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return tc_fail("cuTensorMapEncodeTiled(weights) failed (%d): K=%llu cout=%d bn=%d", (int)r,
+                                        (unsigned long long)ktot, p.cout, op.bn);
+  op.valid = true;
+  *out = op;
+  return 0;
+}
+
+int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s) {
+  if (!op.valid) return tc_fail("conv plan is not valid");
+  TcKernelParams k{};
+  k.bias = p.bias;
+  k.res = reinterpret_cast<const __nv_bfloat16*>(p.res);
+  k.out = reinterpret_cast<__nv_bfloat16*>(p.out);
+  k.M = p.n * p.ho * p.wo;
+  k.ho = p.ho; k.wo = p.wo;
+  k.stride = p.stride; k.pad_h = p.pad_h; k.pad_w = p.pad_w;
+  k.kw = p.kw; k.cpb = op.cpb; k.num_kb = p.kh * p.kw * op.cpb;
+  k.bn = op.bn; k.out_pitch = p.out_pitch; k.res_pitch = p.res_pitch; k.relu = p.relu;
+  k.stages = op.stages; k.tmem_cols = op.tmem_cols;
+  dim3 grid((unsigned)((k.M + BLOCK_M - 1) / BLOCK_M), (unsigned)(p.cout / op.bn));
+  conv_tc_kernel<<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return tc_fail("conv_tc_kernel launch: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t off_input, size_t off_tc, uint8_t* wts,
+            int micro_batch, int max_batch) {
+  (void)off_input; (void)off_tc; (void)max_batch;
+  plan->ops.assign(net.ops.size(), TcOpPlan());
+  plan->micro_batch = micro_batch;
+  for (size_t i = 0; i < net.ops.size(); ++i) {
+    const Op& op = net.ops[i];
+    if (!tc_supported(op)) continue;
+    const Tensor& ti = net.tensors[op.in];
+    const Tensor& to = net.tensors[op.out];
+    if (ti.buf < 0) continue;
+    ConvParams p{};
+    p.in = ws + off_arena + ((size_t)net.bufs[ti.buf].offset * micro_batch + ti.c_off) * 2;
+    p.w = wts + op.wpack_off;
+    p.n = micro_batch; p.hi = ti.h; p.wi = ti.w; p.cin = op.cin; p.in_pitch = ti.c_pitch;
+    p.ho = to.h; p.wo = to.w; p.cout = op.cout; p.out_pitch = to.c_pitch;
+    p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;
+    p.cin_pad = op.cin_pad;
+    if (tc_plan_one(&plan->ops[i], p, micro_batch, TcTune()) != 0) return -1;
+  }
+  return 0;
+}
+
+int launch_conv_tc(const TcPlan& plan, int op_index, const ConvParams& p, int img0, cudaStream_t s, int* nlaunch) {
+  (void)img0;
+  if (op_index < 0 || op_index >= (int)plan.ops.size() || !plan.ops[op_index].valid)
+    return tc_fail("no tcgen05 plan for op %d", op_index);
+  if (nlaunch) *nlaunch = 1;
+  return launch_conv_tc_plan(plan.ops[op_index], p, s);
+}
+
+}  // namespace dml

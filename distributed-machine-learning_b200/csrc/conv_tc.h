@@ -1,0 +1,47 @@
+// conv_tc.h -- tcgen05/TMEM implicit-GEMM convolution fed by TMA (internal).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <vector>
+
+#include "graph.h"
+#include "kernels.h"
+
+namespace dml {
+
+struct TcOpPlan {
+  bool valid = false;
+  alignas(64) CUtensorMap map_a;  // im2col map over the NHWC input view
+  alignas(64) CUtensorMap map_b;  // tiled map over packed weights [cout][taps*cin_pad]
+  int bn = 0;        // N tile (output channels per CTA)
+  int stages = 0;
+  int tmem_cols = 0;
+  int cpb = 0;       // 64-channel blocks per tap
+  size_t smem = 0;
+};
+
+struct TcPlan {
+  std::vector<TcOpPlan> ops;  // indexed like Net::ops
+  int micro_batch = 0;
+};
+
+// Tile-shape overrides for tuning/tests (0 = heuristic).
+struct TcTune {
+  int bn = 0;
+  int stages = 0;
+};
+
+bool tc_supported(const Op& op);
+int tc_init();
+size_t tc_scratch_bytes(const Net& net, int micro_batch);
+int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t off_input, size_t off_tc, uint8_t* wts,
+            int micro_batch, int max_batch);
+// Builds the plan of ONE conv over explicit pointers (tests, tuning).
+int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune& tune);
+int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s);
+int launch_conv_tc(const TcPlan& plan, int op_index, const ConvParams& p, int img0, cudaStream_t s, int* nlaunch);
+const char* tc_last_error();
+
+}  // namespace dml

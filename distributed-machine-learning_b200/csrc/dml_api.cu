@@ -1,0 +1,498 @@
+// dml_api.cu -- the C ABI of libdml_b200.so (include/dml_b200.h): engine
+// object, weight folding/packing, the per-micro-batch layer walk.
+//
+// Replaces what /root/reference/models.py:23-71 does through Keras: model
+// construction (:26, :51), load_img/preprocess_input (:34-38, :59-63),
+// predict (:40, :65) and decode_predictions' top-5 selection (:42, :67).
+#include "../../include/dml_b200.h"
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "conv_tc.h"
+#include "graph.h"
+#include "kernels.h"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                        \
+  do {                                                                                        \
+    cudaError_t err__ = (expr);                                                               \
+    if (err__ != cudaSuccess)                                                                 \
+      return fail(DML_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(err__), __FILE__, __LINE__); \
+  } while (0)
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+uint16_t f32_to_bf16_rn(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);  // NaN
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+
+void make_lut(int mode, float out[768]) {
+  // preprocess_input for uint8 input, per OUTPUT channel (models.py:38 / :63).
+  const float mean_bgr[3] = {103.939f, 116.779f, 123.68f};
+  for (int c = 0; c < 3; ++c)
+    for (int v = 0; v < 256; ++v) {
+      volatile float x = (float)v;
+      if (mode == 0) {
+        x = x - mean_bgr[c];  // caffe: BGR order, mean subtraction only
+      } else {
+        x = x / 127.5f;  // tf: true divide, then subtract (two rounded fp32 ops)
+        x = x - 1.0f;
+      }
+      out[c * 256 + v] = x;
+    }
+}
+
+}  // namespace
+
+struct dml_engine {
+  int device = 0, model = 0, max_batch = 0, micro_batch = 0, flags = 0;
+  bool fp32 = false, use_tc = false, keep_all = false;
+  int act_bytes = 2;
+  dml::Net net;
+  uint8_t* ws = nullptr;
+  size_t ws_bytes = 0;
+  uint8_t* wts = nullptr;
+  size_t wts_bytes = 0;
+  bool weights_loaded = false;
+  size_t off_lut = 0, off_input = 0, off_arena = 0, off_pooled = 0, off_logits = 0, off_tc = 0, ws_need = 0;
+  int64_t launches = 0;
+  dml::TcPlan tc;  // tensor maps etc. for the tcgen05 path
+
+  void* tensor_ptr(int t, int img0) const {
+    const dml::Tensor& tt = net.tensors[t];
+    if (tt.buf == -1) {
+      size_t per = (size_t)net.input_size * net.input_size * 3 * act_bytes;
+      return ws + off_input + per * img0;
+    }
+    if (tt.buf == -2) return ws + off_pooled + (size_t)img0 * tt.c * 4;
+    const dml::Buf& b = net.bufs[tt.buf];
+    return ws + off_arena + ((size_t)b.offset * micro_batch + tt.c_off) * act_bytes;
+  }
+};
+
+namespace {
+
+int check_model(int model) {
+  if (model != DML_MODEL_RESNET50 && model != DML_MODEL_INCEPTIONV3)
+    return fail(DML_EINVAL, "unknown model id %d (0 = ResNet50, 1 = InceptionV3)", model);
+  return 0;
+}
+
+int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
+  const dml::Net& net = e->net;
+  for (size_t oi = 0; oi < net.ops.size(); ++oi) {
+    const dml::Op& op = net.ops[oi];
+    const dml::Tensor& ti = net.tensors[op.in];
+    const dml::Tensor& to = net.tensors[op.out];
+    if (op.kind == dml::OP_CONV) {
+      dml::ConvParams p{};
+      p.in = e->tensor_ptr(op.in, img0);
+      p.w = e->wts + op.wpack_off;
+      p.bias = reinterpret_cast<const float*>(e->wts + op.bias_off);
+      p.res = op.res >= 0 ? e->tensor_ptr(op.res, img0) : nullptr;
+      p.out = e->tensor_ptr(op.out, img0);
+      p.n = cnt; p.hi = ti.h; p.wi = ti.w; p.cin = op.cin; p.in_pitch = ti.c_pitch;
+      p.ho = to.h; p.wo = to.w; p.cout = op.cout; p.out_pitch = to.c_pitch;
+      p.res_pitch = op.res >= 0 ? net.tensors[op.res].c_pitch : 0;
+      p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;
+      p.cin_pad = op.cin_pad; p.relu = op.relu;
+      int nl = 0;
+      if (e->use_tc && dml::tc_supported(op)) {
+        int rc = dml::launch_conv_tc(e->tc, (int)oi, p, img0, s, &nl);
+        if (rc != 0) return fail(DML_ECUDA, "tcgen05 conv launch failed for %s: %s", op.name.c_str(), dml::tc_last_error());
+      } else {
+        dml::launch_conv_naive(p, e->fp32, s);
+        nl = 1;
+      }
+      e->launches += nl;
+    } else if (op.kind == dml::OP_MAXPOOL || op.kind == dml::OP_AVGPOOL) {
+      dml::PoolParams p{};
+      p.in = e->tensor_ptr(op.in, img0);
+      p.out = e->tensor_ptr(op.out, img0);
+      p.n = cnt; p.hi = ti.h; p.wi = ti.w; p.c = ti.c; p.in_pitch = ti.c_pitch;
+      p.ho = to.h; p.wo = to.w; p.out_pitch = to.c_pitch;
+      p.k = op.kh; p.stride = op.stride; p.pad = op.pad_h;
+      if (op.kind == dml::OP_MAXPOOL) dml::launch_maxpool(p, e->fp32, s);
+      else dml::launch_avgpool(p, e->fp32, s);
+      e->launches += 1;
+    } else if (op.kind == dml::OP_GAP) {
+      dml::launch_gap(e->tensor_ptr(op.in, img0), reinterpret_cast<float*>(e->tensor_ptr(op.out, img0)), cnt,
+                      ti.h * ti.w, ti.c, ti.c_pitch, e->fp32, s);
+      e->launches += 1;
+    }
+  }
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int run_head(dml_engine* e, int n, float* d_probs, int32_t* d_idx, float* d_prob, cudaStream_t s) {
+  const dml::Net& net = e->net;
+  const float* pooled = reinterpret_cast<const float*>(e->ws + e->off_pooled);
+  float* logits = reinterpret_cast<float*>(e->ws + e->off_logits);
+  int cin = net.tensors[net.pooled_tensor].c;
+  dml::launch_fc(pooled, reinterpret_cast<const float*>(e->wts + net.fc_w_off),
+                 reinterpret_cast<const float*>(e->wts + net.fc_b_off), logits, n, cin, s);
+  dml::launch_softmax_top5(logits, d_probs, d_idx, d_prob, n, s);
+  e->launches += 2;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int run_pre(dml_engine* e, const uint8_t* d_pixels, const int64_t* d_img_off, const int32_t* d_hw,
+            const int32_t* d_xtab, const int32_t* d_ytab, int img0, int cnt, cudaStream_t s) {
+  dml::PreParams p{};
+  const int S = e->net.input_size;
+  p.pixels = d_pixels;
+  p.img_off = d_img_off + img0;
+  p.hw = d_hw + 2 * img0;
+  p.xtab = d_xtab + (size_t)img0 * S;
+  p.ytab = d_ytab + (size_t)img0 * S;
+  p.out = e->tensor_ptr(e->net.input_tensor, img0);
+  p.n = cnt; p.S = S; p.caffe = e->net.mode == 0;
+  dml::launch_preprocess(p, reinterpret_cast<const float*>(e->ws + e->off_lut), e->fp32, s);
+  e->launches += 1;
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int check_ready(dml_engine* e, int n) {
+  if (!e) return fail(DML_EINVAL, "engine is NULL");
+  if (!e->ws) return fail(DML_ESTATE, "no workspace bound: call dml_bind_workspace first");
+  if (!e->wts || !e->weights_loaded) return fail(DML_ESTATE, "weights not loaded: call dml_bind_weights + dml_load_weights first");
+  if (n < 0 || n > e->max_batch) return fail(DML_ESIZE, "n = %d is outside [0, max_batch = %d]", n, e->max_batch);
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* dml_last_error(void) { return g_err.c_str(); }
+const char* dml_version(void) { return "dml_b200 0.1 (sm_100a)"; }
+
+int dml_model_info(int model, int* input_size, int* preprocess_mode) {
+  if (int rc = check_model(model)) return rc;
+  if (input_size) *input_size = model == DML_MODEL_RESNET50 ? 224 : 299;
+  if (preprocess_mode) *preprocess_mode = model == DML_MODEL_RESNET50 ? 0 : 1;
+  return 0;
+}
+
+int dml_model_num_weights(int model, int* num_arrays, int64_t* total_floats) {
+  if (int rc = check_model(model)) return rc;
+  dml::Net net;
+  std::string err;
+  if (!dml::build_weight_spec(model, &net, &err)) return fail(DML_EINVAL, "%s", err.c_str());
+  if (num_arrays) *num_arrays = (int)net.warr.size();
+  if (total_floats) *total_floats = net.total_floats;
+  return 0;
+}
+
+int dml_model_weight_info(int model, int i, char* name, int name_cap, int64_t shape[4], int* rank) {
+  if (int rc = check_model(model)) return rc;
+  dml::Net net;
+  std::string err;
+  if (!dml::build_weight_spec(model, &net, &err)) return fail(DML_EINVAL, "%s", err.c_str());
+  if (i < 0 || i >= (int)net.warr.size()) return fail(DML_EINVAL, "weight index %d out of range [0, %zu)", i, net.warr.size());
+  const dml::WeightArr& a = net.warr[i];
+  if (name && name_cap > 0) snprintf(name, name_cap, "%s", a.name.c_str());
+  if (shape) for (int d = 0; d < 4; ++d) shape[d] = a.shape[d];
+  if (rank) *rank = a.rank;
+  return 0;
+}
+
+int dml_preprocess_lut(int model, float out[768]) {
+  if (int rc = check_model(model)) return rc;
+  if (!out) return fail(DML_EINVAL, "out is NULL");
+  make_lut(model == DML_MODEL_RESNET50 ? 0 : 1, out);
+  return 0;
+}
+
+int dml_create(int device, int model, int max_batch, int micro_batch, int flags, dml_engine** out) {
+  if (!out) return fail(DML_EINVAL, "out is NULL");
+  *out = nullptr;
+  if (int rc = check_model(model)) return rc;
+  if (max_batch < 1 || max_batch > 4096) return fail(DML_ESIZE, "max_batch = %d is outside [1, 4096]", max_batch);
+  if (micro_batch < 0) return fail(DML_EINVAL, "micro_batch = %d is negative", micro_batch);
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev == 0)
+    return fail(DML_ECUDA, "no CUDA device available (%s): this library has no CPU fallback", cudaGetErrorString(ce));
+  if (device < 0 || device >= ndev) return fail(DML_EINVAL, "device %d out of range [0, %d)", device, ndev);
+  CUDA_TRY(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return fail(DML_ECUDA, "device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major, prop.minor);
+
+  dml_engine* e = new dml_engine();
+  e->device = device; e->model = model; e->max_batch = max_batch; e->flags = flags;
+  e->fp32 = (flags & DML_FLAG_FP32_CHECK) != 0;
+  e->use_tc = !e->fp32 && (flags & DML_FLAG_NO_TENSOR_CORE) == 0;
+  e->keep_all = (flags & DML_FLAG_KEEP_ALL) != 0;
+  e->act_bytes = e->fp32 ? 4 : 2;
+  if (micro_batch == 0) micro_batch = 32;
+  e->micro_batch = micro_batch < max_batch ? micro_batch : max_batch;
+  std::string err;
+  if (!dml::build_net(model, e->keep_all, e->fp32 ? 4 : 2, !e->fp32, &e->net, &err)) {
+    delete e;
+    return fail(DML_EINVAL, "%s", err.c_str());
+  }
+  const dml::Net& net = e->net;
+  size_t off = 0;
+  e->off_lut = off; off = align_up(off + 768 * 4, 256);
+  e->off_input = off; off = align_up(off + (size_t)max_batch * net.input_size * net.input_size * 3 * e->act_bytes + 64, 256);
+  e->off_arena = off; off = align_up(off + (size_t)net.arena_elems * e->micro_batch * e->act_bytes, 256);
+  e->off_pooled = off; off = align_up(off + (size_t)max_batch * net.tensors[net.pooled_tensor].c * 4, 256);
+  e->off_logits = off; off = align_up(off + (size_t)max_batch * 1000 * 4, 256);
+  e->off_tc = off; off = align_up(off + dml::tc_scratch_bytes(net, e->micro_batch), 256);
+  e->ws_need = off;
+  dml::init_kernels();
+  if (e->use_tc) {
+    if (dml::tc_init() != 0) {
+      std::string m = dml::tc_last_error();
+      delete e;
+      return fail(DML_ECUDA, "tcgen05 path init failed: %s", m.c_str());
+    }
+  }
+  *out = e;
+  return 0;
+}
+
+void dml_destroy(dml_engine* e) { delete e; }
+
+int dml_workspace_bytes(dml_engine* e, size_t* bytes) {
+  if (!e || !bytes) return fail(DML_EINVAL, "NULL argument");
+  *bytes = e->ws_need;
+  return 0;
+}
+int dml_weights_bytes(dml_engine* e, size_t* bytes) {
+  if (!e || !bytes) return fail(DML_EINVAL, "NULL argument");
+  *bytes = (size_t)e->net.weights_bytes;
+  return 0;
+}
+
+int dml_bind_workspace(dml_engine* e, void* dev_ptr, size_t bytes) {
+  if (!e || !dev_ptr) return fail(DML_EINVAL, "NULL argument");
+  if (bytes < e->ws_need) return fail(DML_ESIZE, "workspace of %zu bytes is smaller than the %zu required", bytes, e->ws_need);
+  if ((uintptr_t)dev_ptr % 256) return fail(DML_EINVAL, "workspace pointer must be 256-byte aligned");
+  CUDA_TRY(cudaSetDevice(e->device));
+  e->ws = reinterpret_cast<uint8_t*>(dev_ptr);
+  e->ws_bytes = bytes;
+  float lut[768];
+  make_lut(e->net.mode, lut);
+  CUDA_TRY(cudaMemcpy(e->ws + e->off_lut, lut, sizeof lut, cudaMemcpyHostToDevice));
+  // Activation arena starts at zero so that padded/unused lanes are finite.
+  CUDA_TRY(cudaMemset(e->ws + e->off_input, 0, e->ws_need - e->off_input));
+  if (e->use_tc && e->wts) {
+    if (dml::tc_plan(&e->tc, e->net, e->ws, e->off_arena, e->off_input, e->off_tc, e->wts, e->micro_batch, e->max_batch) != 0)
+      return fail(DML_ECUDA, "tcgen05 plan failed: %s", dml::tc_last_error());
+  }
+  return 0;
+}
+
+int dml_bind_weights(dml_engine* e, void* dev_ptr, size_t bytes) {
+  if (!e || !dev_ptr) return fail(DML_EINVAL, "NULL argument");
+  if (bytes < (size_t)e->net.weights_bytes)
+    return fail(DML_ESIZE, "weights buffer of %zu bytes is smaller than the %lld required", bytes, (long long)e->net.weights_bytes);
+  if ((uintptr_t)dev_ptr % 256) return fail(DML_EINVAL, "weights pointer must be 256-byte aligned");
+  e->wts = reinterpret_cast<uint8_t*>(dev_ptr);
+  e->wts_bytes = bytes;
+  e->weights_loaded = false;
+  if (e->use_tc && e->ws) {
+    CUDA_TRY(cudaSetDevice(e->device));
+    if (dml::tc_plan(&e->tc, e->net, e->ws, e->off_arena, e->off_input, e->off_tc, e->wts, e->micro_batch, e->max_batch) != 0)
+      return fail(DML_ECUDA, "tcgen05 plan failed: %s", dml::tc_last_error());
+  }
+  return 0;
+}
+
+int dml_load_weights(dml_engine* e, const float* blob, size_t num_floats) {
+  if (!e || !blob) return fail(DML_EINVAL, "NULL argument");
+  if (!e->wts) return fail(DML_ESTATE, "no weights buffer bound: call dml_bind_weights first");
+  const dml::Net& net = e->net;
+  if ((int64_t)num_floats != net.total_floats)
+    return fail(DML_ESIZE, "weight blob has %zu floats, model needs %lld", num_floats, (long long)net.total_floats);
+  CUDA_TRY(cudaSetDevice(e->device));
+  std::vector<uint8_t> host((size_t)net.weights_bytes, 0);
+  for (const dml::Op& op : net.ops) {
+    if (op.kind != dml::OP_CONV) continue;
+    const float* K = blob + net.warr[op.w_kernel].offset;  // HWIO
+    const float* bias = op.w_bias >= 0 ? blob + net.warr[op.w_bias].offset : nullptr;
+    const float* gamma = op.w_gamma >= 0 ? blob + net.warr[op.w_gamma].offset : nullptr;
+    const float* beta = blob + net.warr[op.w_beta].offset;
+    const float* mean = blob + net.warr[op.w_mean].offset;
+    const float* var = blob + net.warr[op.w_var].offset;
+    const int taps = op.kh * op.kw;
+    float* bout = reinterpret_cast<float*>(host.data() + op.bias_off);
+    for (int co = 0; co < op.cout; ++co) {
+      // BN folded into the conv: s = gamma / sqrt(var + eps); W' = W*s; b' = beta + (b - mean)*s
+      double s = (gamma ? (double)gamma[co] : 1.0) / std::sqrt((double)var[co] + (double)op.eps);
+      bout[co] = (float)((double)beta[co] + ((bias ? (double)bias[co] : 0.0) - (double)mean[co]) * s);
+      for (int t = 0; t < taps; ++t)
+        for (int c = 0; c < op.cin; ++c) {
+          float v = (float)((double)K[((size_t)t * op.cin + c) * op.cout + co] * s);
+          size_t idx = ((size_t)co * taps + t) * op.cin_pad + c;
+          if (e->fp32) reinterpret_cast<float*>(host.data() + op.wpack_off)[idx] = v;
+          else reinterpret_cast<uint16_t*>(host.data() + op.wpack_off)[idx] = f32_to_bf16_rn(v);
+        }
+    }
+  }
+  memcpy(host.data() + net.fc_w_off, blob + net.warr[net.fc_kernel].offset, (size_t)net.warr[net.fc_kernel].count * 4);
+  memcpy(host.data() + net.fc_b_off, blob + net.warr[net.fc_bias].offset, 1000 * 4);
+  CUDA_TRY(cudaMemcpy(e->wts, host.data(), host.size(), cudaMemcpyHostToDevice));
+  e->weights_loaded = true;
+  return 0;
+}
+
+int dml_weights_ready(dml_engine* e) {
+  if (!e) return fail(DML_EINVAL, "engine is NULL");
+  if (!e->wts) return fail(DML_ESTATE, "no weights buffer bound");
+  e->weights_loaded = true;
+  return 0;
+}
+
+int dml_preprocess(dml_engine* e, const uint8_t* d_pixels, const int64_t* d_img_off, const int32_t* d_hw,
+                   const int32_t* d_xtab, const int32_t* d_ytab, int n, void* stream) {
+  if (!e) return fail(DML_EINVAL, "engine is NULL");
+  if (!e->ws) return fail(DML_ESTATE, "no workspace bound: call dml_bind_workspace first");
+  if (n < 0 || n > e->max_batch) return fail(DML_ESIZE, "n = %d is outside [0, max_batch = %d]", n, e->max_batch);
+  if (n == 0) return 0;
+  if (!d_pixels || !d_img_off || !d_hw || !d_xtab || !d_ytab) return fail(DML_EINVAL, "NULL device pointer");
+  CUDA_TRY(cudaSetDevice(e->device));
+  return run_pre(e, d_pixels, d_img_off, d_hw, d_xtab, d_ytab, 0, n, (cudaStream_t)stream);
+}
+
+int dml_forward(dml_engine* e, int n, float* d_probs, int32_t* d_top5_idx, float* d_top5_prob, void* stream) {
+  if (int rc = check_ready(e, n)) return rc;
+  if (n == 0) return 0;
+  if (!d_top5_idx || !d_top5_prob) return fail(DML_EINVAL, "NULL output pointer");
+  CUDA_TRY(cudaSetDevice(e->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  for (int i0 = 0; i0 < n; i0 += e->micro_batch) {
+    int cnt = n - i0 < e->micro_batch ? n - i0 : e->micro_batch;
+    if (int rc = run_layers(e, i0, cnt, s)) return rc;
+  }
+  return run_head(e, n, d_probs, d_top5_idx, d_top5_prob, s);
+}
+
+int dml_infer(dml_engine* e, const uint8_t* d_pixels, const int64_t* d_img_off, const int32_t* d_hw,
+              const int32_t* d_xtab, const int32_t* d_ytab, int n, float* d_probs, int32_t* d_top5_idx,
+              float* d_top5_prob, void* stream) {
+  if (int rc = check_ready(e, n)) return rc;
+  if (n == 0) return 0;
+  if (!d_pixels || !d_img_off || !d_hw || !d_xtab || !d_ytab) return fail(DML_EINVAL, "NULL device pointer");
+  if (!d_top5_idx || !d_top5_prob) return fail(DML_EINVAL, "NULL output pointer");
+  CUDA_TRY(cudaSetDevice(e->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  for (int i0 = 0; i0 < n; i0 += e->micro_batch) {
+    int cnt = n - i0 < e->micro_batch ? n - i0 : e->micro_batch;
+    if (int rc = run_pre(e, d_pixels, d_img_off, d_hw, d_xtab, d_ytab, i0, cnt, s)) return rc;
+    if (int rc = run_layers(e, i0, cnt, s)) return rc;
+  }
+  return run_head(e, n, d_probs, d_top5_idx, d_top5_prob, s);
+}
+
+int dml_num_tensors(dml_engine* e, int* n) {
+  if (!e || !n) return fail(DML_EINVAL, "NULL argument");
+  *n = (int)e->net.tensors.size();
+  return 0;
+}
+
+int dml_tensor_info(dml_engine* e, int i, char* name, int name_cap, int* h, int* w, int* c, void** dev_ptr,
+                    int* c_pitch, int* elem_bytes, int* keep) {
+  if (!e) return fail(DML_EINVAL, "engine is NULL");
+  if (i < 0 || i >= (int)e->net.tensors.size()) return fail(DML_EINVAL, "tensor index %d out of range", i);
+  const dml::Tensor& t = e->net.tensors[i];
+  if (name && name_cap > 0) snprintf(name, name_cap, "%s", t.name.c_str());
+  if (h) *h = t.h;
+  if (w) *w = t.w;
+  if (c) *c = t.c;
+  if (dev_ptr) *dev_ptr = e->ws ? e->tensor_ptr(i, 0) : nullptr;
+  if (c_pitch) *c_pitch = t.c_pitch;
+  if (elem_bytes) *elem_bytes = t.buf == -2 ? 4 : e->act_bytes;
+  if (keep) *keep = e->keep_all || t.buf < 0;
+  return 0;
+}
+
+int dml_input_tensor(dml_engine* e, void** dev_ptr, int* elem_bytes) {
+  if (!e || !dev_ptr) return fail(DML_EINVAL, "NULL argument");
+  if (!e->ws) return fail(DML_ESTATE, "no workspace bound");
+  *dev_ptr = e->ws + e->off_input;
+  if (elem_bytes) *elem_bytes = e->act_bytes;
+  return 0;
+}
+
+int dml_logits(dml_engine* e, float** dev_ptr) {
+  if (!e || !dev_ptr) return fail(DML_EINVAL, "NULL argument");
+  if (!e->ws) return fail(DML_ESTATE, "no workspace bound");
+  *dev_ptr = reinterpret_cast<float*>(e->ws + e->off_logits);
+  return 0;
+}
+
+int dml_launch_count(dml_engine* e, int64_t* launches) {
+  if (!e || !launches) return fail(DML_EINVAL, "NULL argument");
+  *launches = e->launches;
+  return 0;
+}
+
+int dml_conv2d_bf16(int impl, const void* d_in, const void* d_w, const float* d_bias, const void* d_res, void* d_out,
+                    int n, int hi, int wi, int cin, int in_pitch, int cout, int out_pitch, int res_pitch, int kh,
+                    int kw, int stride, int pad_h, int pad_w, int cin_pad, int relu, int tile_n, int stages,
+                    void* stream) {
+  if (!d_in || !d_w || !d_bias || !d_out) return fail(DML_EINVAL, "NULL device pointer");
+  if (n < 1 || stride < 1 || kh < 1 || kw < 1) return fail(DML_EINVAL, "bad conv geometry");
+  dml::ConvParams p{};
+  p.in = d_in; p.w = d_w; p.bias = d_bias; p.res = d_res; p.out = d_out;
+  p.n = n; p.hi = hi; p.wi = wi; p.cin = cin; p.in_pitch = in_pitch;
+  p.ho = (hi + 2 * pad_h - kh) / stride + 1;
+  p.wo = (wi + 2 * pad_w - kw) / stride + 1;
+  p.cout = cout; p.out_pitch = out_pitch; p.res_pitch = res_pitch;
+  p.kh = kh; p.kw = kw; p.stride = stride; p.pad_h = pad_h; p.pad_w = pad_w; p.cin_pad = cin_pad; p.relu = relu;
+  if (impl == 0) {
+    dml::launch_conv_naive(p, false, (cudaStream_t)stream);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+  }
+  if (impl != 1) return fail(DML_EINVAL, "impl must be 0 (CUDA cores) or 1 (tcgen05)");
+  if (dml::tc_init() != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
+  dml::TcOpPlan plan;
+  dml::TcTune tune;
+  tune.bn = tile_n; tune.stages = stages;
+  if (dml::tc_plan_one(&plan, p, n, tune) != 0) return fail(DML_EINVAL, "%s", dml::tc_last_error());
+  if (dml::launch_conv_tc_plan(plan, p, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
+  return 0;
+}
+
+int dml_sync(dml_engine* e) {
+  if (!e) return fail(DML_EINVAL, "engine is NULL");
+  CUDA_TRY(cudaSetDevice(e->device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  return 0;
+}
+
+}  // extern "C"

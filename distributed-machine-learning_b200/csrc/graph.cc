@@ -1,0 +1,352 @@
+// graph.cc -- ResNet50 / InceptionV3 as the reference's Keras builds them
+// (/root/reference/models.py:26 InceptionV3(...), :51 ResNet50(...)); layer
+// semantics restated from the published keras.applications definitions
+// (SURVEY.md Appendix A/B).  Weight arrays are listed in layer creation order,
+// each layer in get_weights() order.
+#include "graph.h"
+
+#include <algorithm>
+#include <cstdio>
+
+namespace dml {
+namespace {
+
+struct Builder {
+  Net* net;
+  bool keep_all;
+  int nconv = 0;  // InceptionV3 auto-naming counter
+
+  int add_warr(const std::string& name, std::initializer_list<int64_t> shape) {
+    WeightArr a;
+    a.name = name;
+    a.rank = (int)shape.size();
+    int i = 0;
+    a.count = 1;
+    for (int64_t s : shape) { a.shape[i++] = s; a.count *= s; }
+    a.offset = net->total_floats;
+    net->total_floats += a.count;
+    net->warr.push_back(a);
+    return (int)net->warr.size() - 1;
+  }
+
+  int new_buf(int h, int w, int c) {
+    Buf b;
+    b.elems = (int64_t)h * w * c;
+    net->bufs.push_back(b);
+    return (int)net->bufs.size() - 1;
+  }
+  int new_tensor(const std::string& name, int h, int w, int c) {
+    Tensor t;
+    t.name = name; t.h = h; t.w = w; t.c = c;
+    t.buf = new_buf(h, w, c);
+    t.c_off = 0; t.c_pitch = c;
+    net->tensors.push_back(t);
+    return (int)net->tensors.size() - 1;
+  }
+  int view(int parent, const std::string& name, int c_off, int c) {
+    Tensor t = net->tensors[parent];
+    t.name = name; t.c_off = c_off; t.c = c;
+    net->tensors.push_back(t);
+    return (int)net->tensors.size() - 1;
+  }
+  void touch(int tensor, int op_index) {
+    int b = net->tensors[tensor].buf;
+    if (b < 0) return;
+    net->bufs[b].first_use = std::min(net->bufs[b].first_use, op_index);
+    net->bufs[b].last_use = std::max(net->bufs[b].last_use, op_index);
+  }
+  int push(Op op) {
+    int idx = (int)net->ops.size();
+    touch(op.in, idx);
+    touch(op.out, idx);
+    if (op.res >= 0) touch(op.res, idx);
+    net->ops.push_back(op);
+    return idx;
+  }
+
+  // Conv2D (+bias) + BatchNormalization (+ReLU) (+residual add before the ReLU).
+  // out < 0: a fresh tensor is created.  Returns the output tensor id.
+  int conv(int in, int out, const std::string& cname, const std::string& bname, int cout, int kh, int kw,
+           int stride, bool same, bool bias, bool bn_scale, float eps, bool relu, int res) {
+    const Tensor ti = net->tensors[in];
+    Op op;
+    op.kind = OP_CONV; op.name = cname;
+    op.kh = kh; op.kw = kw; op.stride = stride;
+    op.pad_h = same ? (kh - 1) / 2 : 0;
+    op.pad_w = same ? (kw - 1) / 2 : 0;
+    int ho = (ti.h + 2 * op.pad_h - kh) / stride + 1;
+    int wo = (ti.w + 2 * op.pad_w - kw) / stride + 1;
+    op.cin = ti.c; op.cout = cout;
+    op.w_kernel = add_warr(cname + "/kernel", {kh, kw, ti.c, cout});
+    if (bias) op.w_bias = add_warr(cname + "/bias", {cout});
+    if (bn_scale) op.w_gamma = add_warr(bname + "/gamma", {cout});
+    op.w_beta = add_warr(bname + "/beta", {cout});
+    op.w_mean = add_warr(bname + "/moving_mean", {cout});
+    op.w_var = add_warr(bname + "/moving_variance", {cout});
+    op.eps = eps; op.relu = relu; op.res = res;
+    if (out < 0) out = new_tensor(cname + ":out", ho, wo, cout);
+    op.in = in; op.out = out;
+    net->conv_macs += (int64_t)ho * wo * cout * kh * kw * ti.c;
+    push(op);
+    return out;
+  }
+  int pool(OpKind kind, int in, int out, const std::string& name, int k, int stride, int pad) {
+    const Tensor ti = net->tensors[in];
+    Op op;
+    op.kind = kind; op.name = name;
+    op.kh = op.kw = k; op.stride = stride; op.pad_h = op.pad_w = pad;
+    int ho = (ti.h + 2 * pad - k) / stride + 1, wo = (ti.w + 2 * pad - k) / stride + 1;
+    if (out < 0) out = new_tensor(name + ":out", ho, wo, ti.c);
+    op.in = in; op.out = out; op.cin = op.cout = ti.c;
+    push(op);
+    return out;
+  }
+  // InceptionV3 conv2d_bn: Conv2D(no bias) -> BN(scale=False, eps 1e-3) -> ReLU
+  int cb(int in, int out, int f, int kh, int kw, bool same = true, int stride = 1) {
+    int i = nconv++;
+    std::string cn = i == 0 ? "conv2d" : "conv2d_" + std::to_string(i);
+    std::string bn = i == 0 ? "batch_normalization" : "batch_normalization_" + std::to_string(i);
+    return conv(in, out, cn, bn, f, kh, kw, stride, same, false, false, 1e-3f, true, -1);
+  }
+  void head(int x) {
+    const Tensor t = net->tensors[x];
+    Op op;
+    op.kind = OP_GAP; op.name = "avg_pool";
+    op.in = x; op.cin = op.cout = t.c;
+    Tensor p;
+    p.name = "avg_pool"; p.h = 1; p.w = 1; p.c = t.c; p.buf = -2; p.c_pitch = t.c;
+    net->tensors.push_back(p);
+    op.out = net->pooled_tensor = (int)net->tensors.size() - 1;
+    push(op);
+    net->fc_kernel = add_warr("predictions/kernel", {t.c, 1000});
+    net->fc_bias = add_warr("predictions/bias", {1000});
+  }
+};
+
+void build_resnet50(Builder& b) {
+  Net* net = b.net;
+  const float eps = 1.001e-5f;
+  int x = net->input_tensor;
+  // conv1_pad(3) + conv1_conv 7x7 s2 valid == 7x7 s2 with zero padding 3 -> 112x112
+  {
+    const Tensor ti = net->tensors[x];
+    Op op;
+    op.kind = OP_CONV; op.name = "conv1_conv";
+    op.kh = op.kw = 7; op.stride = 2; op.pad_h = op.pad_w = 3;
+    op.cin = 3; op.cout = 64;
+    op.w_kernel = b.add_warr("conv1_conv/kernel", {7, 7, 3, 64});
+    op.w_bias = b.add_warr("conv1_conv/bias", {64});
+    op.w_gamma = b.add_warr("conv1_bn/gamma", {64});
+    op.w_beta = b.add_warr("conv1_bn/beta", {64});
+    op.w_mean = b.add_warr("conv1_bn/moving_mean", {64});
+    op.w_var = b.add_warr("conv1_bn/moving_variance", {64});
+    op.eps = eps; op.relu = true;
+    int ho = (ti.h + 6 - 7) / 2 + 1;
+    op.in = x; op.out = b.new_tensor("conv1_relu", ho, ho, 64);
+    net->conv_macs += (int64_t)ho * ho * 64 * 49 * 3;
+    b.push(op);
+    x = op.out;
+  }
+  // pool1_pad(1, zeros) + MaxPooling2D(3, 2, valid) -> 56x56
+  x = b.pool(OP_MAXPOOL, x, -1, "pool1_pool", 3, 2, 1);
+  net->tensors[x].name = "pool1_pool";
+  const int filters[4] = {64, 128, 256, 512}, blocks[4] = {3, 4, 6, 3}, stride1[4] = {1, 2, 2, 2};
+  for (int s = 0; s < 4; ++s) {
+    int f = filters[s];
+    for (int blk = 1; blk <= blocks[s]; ++blk) {
+      std::string n = "conv" + std::to_string(s + 2) + "_block" + std::to_string(blk);
+      int stride = blk == 1 ? stride1[s] : 1;
+      int sc = x;
+      if (blk == 1) sc = b.conv(x, -1, n + "_0_conv", n + "_0_bn", 4 * f, 1, 1, stride, false, true, true, eps, false, -1);
+      int y = b.conv(x, -1, n + "_1_conv", n + "_1_bn", f, 1, 1, stride, false, true, true, eps, true, -1);
+      y = b.conv(y, -1, n + "_2_conv", n + "_2_bn", f, 3, 3, 1, true, true, true, eps, true, -1);
+      x = b.conv(y, -1, n + "_3_conv", n + "_3_bn", 4 * f, 1, 1, 1, false, true, true, eps, true, sc);
+      net->tensors[x].name = n + "_out";
+    }
+  }
+  b.head(x);
+}
+
+void build_inception_v3(Builder& b) {
+  Net* net = b.net;
+  int x = net->input_tensor;
+  x = b.cb(x, -1, 32, 3, 3, false, 2);
+  net->tensors[x].name = "stem_conv0";
+  x = b.cb(x, -1, 32, 3, 3, false);
+  x = b.cb(x, -1, 64, 3, 3);
+  x = b.pool(OP_MAXPOOL, x, -1, "max_pooling2d", 3, 2, 0);
+  x = b.cb(x, -1, 80, 1, 1, false);
+  x = b.cb(x, -1, 192, 3, 3, false);
+  x = b.pool(OP_MAXPOOL, x, -1, "max_pooling2d_1", 3, 2, 0);
+  net->tensors[x].name = "stem_pool2";
+
+  const int pool_f[3] = {32, 64, 64};
+  for (int i = 0; i < 3; ++i) {  // mixed0..2, 35x35
+    std::string n = "mixed" + std::to_string(i);
+    const Tensor tx = net->tensors[x];
+    int cat = b.new_tensor(n, tx.h, tx.w, 64 + 64 + 96 + pool_f[i]);
+    b.cb(x, b.view(cat, n + ":b1", 0, 64), 64, 1, 1);
+    int t = b.cb(x, -1, 48, 1, 1);
+    b.cb(t, b.view(cat, n + ":b5", 64, 64), 64, 5, 5);
+    t = b.cb(x, -1, 64, 1, 1);
+    t = b.cb(t, -1, 96, 3, 3);
+    b.cb(t, b.view(cat, n + ":b3d", 128, 96), 96, 3, 3);
+    t = b.pool(OP_AVGPOOL, x, -1, n + ":avgpool", 3, 1, 1);
+    b.cb(t, b.view(cat, n + ":bp", 224, pool_f[i]), pool_f[i], 1, 1);
+    x = cat;
+  }
+  {  // mixed3, 17x17
+    const Tensor tx = net->tensors[x];
+    int ho = (tx.h - 3) / 2 + 1;
+    int cat = b.new_tensor("mixed3", ho, ho, 384 + 96 + tx.c);
+    b.cb(x, b.view(cat, "mixed3:b3", 0, 384), 384, 3, 3, false, 2);
+    int t = b.cb(x, -1, 64, 1, 1);
+    t = b.cb(t, -1, 96, 3, 3);
+    b.cb(t, b.view(cat, "mixed3:b3d", 384, 96), 96, 3, 3, false, 2);
+    b.pool(OP_MAXPOOL, x, b.view(cat, "mixed3:bp", 480, tx.c), "max_pooling2d_2", 3, 2, 0);
+    x = cat;
+  }
+  const int c7[4] = {128, 160, 160, 192};
+  for (int i = 0; i < 4; ++i) {  // mixed4..7, 17x17
+    std::string n = "mixed" + std::to_string(i + 4);
+    const Tensor tx = net->tensors[x];
+    int c = c7[i];
+    int cat = b.new_tensor(n, tx.h, tx.w, 768);
+    b.cb(x, b.view(cat, n + ":b1", 0, 192), 192, 1, 1);
+    int t = b.cb(x, -1, c, 1, 1);
+    t = b.cb(t, -1, c, 1, 7);
+    b.cb(t, b.view(cat, n + ":b7", 192, 192), 192, 7, 1);
+    t = b.cb(x, -1, c, 1, 1);
+    t = b.cb(t, -1, c, 7, 1);
+    t = b.cb(t, -1, c, 1, 7);
+    t = b.cb(t, -1, c, 7, 1);
+    b.cb(t, b.view(cat, n + ":b7d", 384, 192), 192, 1, 7);
+    t = b.pool(OP_AVGPOOL, x, -1, n + ":avgpool", 3, 1, 1);
+    b.cb(t, b.view(cat, n + ":bp", 576, 192), 192, 1, 1);
+    x = cat;
+  }
+  {  // mixed8, 8x8
+    const Tensor tx = net->tensors[x];
+    int ho = (tx.h - 3) / 2 + 1;
+    int cat = b.new_tensor("mixed8", ho, ho, 320 + 192 + tx.c);
+    int t = b.cb(x, -1, 192, 1, 1);
+    b.cb(t, b.view(cat, "mixed8:b3", 0, 320), 320, 3, 3, false, 2);
+    t = b.cb(x, -1, 192, 1, 1);
+    t = b.cb(t, -1, 192, 1, 7);
+    t = b.cb(t, -1, 192, 7, 1);
+    b.cb(t, b.view(cat, "mixed8:b7x3", 320, 192), 192, 3, 3, false, 2);
+    b.pool(OP_MAXPOOL, x, b.view(cat, "mixed8:bp", 512, tx.c), "max_pooling2d_3", 3, 2, 0);
+    x = cat;
+  }
+  for (int i = 9; i <= 10; ++i) {  // mixed9, mixed10, 8x8
+    std::string n = "mixed" + std::to_string(i);
+    const Tensor tx = net->tensors[x];
+    int cat = b.new_tensor(n, tx.h, tx.w, 2048);
+    b.cb(x, b.view(cat, n + ":b1", 0, 320), 320, 1, 1);
+    int t = b.cb(x, -1, 384, 1, 1);
+    b.cb(t, b.view(cat, n + ":b3a", 320, 384), 384, 1, 3);
+    b.cb(t, b.view(cat, n + ":b3b", 704, 384), 384, 3, 1);
+    t = b.cb(x, -1, 448, 1, 1);
+    t = b.cb(t, -1, 384, 3, 3);
+    b.cb(t, b.view(cat, n + ":bda", 1088, 384), 384, 1, 3);
+    b.cb(t, b.view(cat, n + ":bdb", 1472, 384), 384, 3, 1);
+    t = b.pool(OP_AVGPOOL, x, -1, n + ":avgpool", 3, 1, 1);
+    b.cb(t, b.view(cat, n + ":bp", 1856, 192), 192, 1, 1);
+    x = cat;
+  }
+  b.head(x);
+}
+
+int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+// Greedy first-fit arena plan: two buffers may overlap in address only if
+// their [first_use, last_use] op ranges are disjoint.
+void plan_arena(Net* net, bool keep_all) {
+  const int nb = (int)net->bufs.size();
+  std::vector<int> order(nb);
+  for (int i = 0; i < nb; ++i) order[i] = i;
+  std::stable_sort(order.begin(), order.end(),
+                   [&](int a, int b) { return net->bufs[a].first_use < net->bufs[b].first_use; });
+  std::vector<int> placed;
+  int64_t top = 0;
+  for (int bi : order) {
+    Buf& b = net->bufs[bi];
+    int64_t sz = align_up(b.elems, 64);
+    int64_t off = 0;
+    if (keep_all) {
+      off = top;
+    } else {
+      // candidate offsets: 0 and the end of every conflicting placed buffer
+      std::vector<std::pair<int64_t, int64_t>> busy;  // [start, end)
+      for (int pj : placed) {
+        const Buf& p = net->bufs[pj];
+        bool live_overlap = !(p.last_use < b.first_use || b.last_use < p.first_use);
+        if (live_overlap) busy.push_back({p.offset, p.offset + align_up(p.elems, 64)});
+      }
+      std::sort(busy.begin(), busy.end());
+      for (auto& iv : busy) {
+        if (off + sz <= iv.first) break;
+        off = std::max(off, iv.second);
+      }
+    }
+    b.offset = off;
+    top = std::max(top, off + sz);
+    placed.push_back(bi);
+  }
+  net->arena_elems = top;
+}
+
+void plan_weights(Net* net, int wbytes, bool tc_pad) {
+  int64_t off = 0;
+  for (Op& op : net->ops) {
+    if (op.kind != OP_CONV) continue;
+    op.cin_pad = (tc_pad && op.cin >= 16) ? (int)align_up(op.cin, 64) : op.cin;
+    op.wpack_off = off;
+    off = align_up(off + (int64_t)op.cout * op.kh * op.kw * op.cin_pad * wbytes, 256);
+    op.bias_off = off;
+    off = align_up(off + (int64_t)op.cout * 4, 256);
+  }
+  const WeightArr& fk = net->warr[net->fc_kernel];
+  net->fc_w_off = off;
+  off = align_up(off + fk.count * 4, 256);
+  net->fc_b_off = off;
+  off = align_up(off + 1000 * 4, 256);
+  net->weights_bytes = off;
+}
+
+bool build(int model, bool keep_all, int wbytes, bool tc_pad, bool spec_only, Net* net, std::string* err) {
+  *net = Net();
+  net->model = model;
+  Builder b{net, keep_all};
+  Tensor in;
+  in.name = "input";
+  in.buf = -1;
+  in.c = 3; in.c_pitch = 3;
+  if (model == 0) {
+    net->input_size = 224; net->mode = 0;
+  } else if (model == 1) {
+    net->input_size = 299; net->mode = 1;
+  } else {
+    if (err) *err = "unknown model id " + std::to_string(model) + " (0 = ResNet50, 1 = InceptionV3)";
+    return false;
+  }
+  in.h = in.w = net->input_size;
+  net->tensors.push_back(in);
+  net->input_tensor = 0;
+  if (model == 0) build_resnet50(b); else build_inception_v3(b);
+  if (spec_only) return true;
+  plan_arena(net, keep_all);
+  plan_weights(net, wbytes, tc_pad);
+  return true;
+}
+
+}  // namespace
+
+bool build_net(int model, bool keep_all, int wbytes, bool tc_pad, Net* net, std::string* err) {
+  return build(model, keep_all, wbytes, tc_pad, false, net, err);
+}
+bool build_weight_spec(int model, Net* net, std::string* err) {
+  return build(model, true, 4, false, true, net, err);
+}
+
+}  // namespace dml

@@ -1,0 +1,77 @@
+// graph.h -- host-side description of the two networks the reference runs
+// (keras.applications ResNet50 / InceptionV3, built at /root/reference/models.py:26,:51):
+// tensors, ops, Keras-layout weight arrays and the activation-arena plan.
+// Pure host C++, no CUDA.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace dml {
+
+struct WeightArr {
+  std::string name;
+  int rank = 0;
+  int64_t shape[4] = {1, 1, 1, 1};
+  int64_t offset = 0;  // floats into the blob
+  int64_t count = 0;
+};
+
+struct Buf {
+  int64_t elems = 0;      // per image
+  int first_use = 1 << 30, last_use = -1;
+  int64_t offset = 0;     // per-image element offset inside the arena
+};
+
+struct Tensor {
+  std::string name;
+  int h = 0, w = 0, c = 0;
+  int buf = -1;     // -1: the engine's input tensor
+  int c_off = 0;    // channel offset inside the buffer (concat views)
+  int c_pitch = 0;  // channels per pixel of the buffer
+};
+
+enum OpKind { OP_CONV = 0, OP_MAXPOOL = 1, OP_AVGPOOL = 2, OP_GAP = 3 };
+
+struct Op {
+  OpKind kind = OP_CONV;
+  std::string name;
+  int in = -1, out = -1, res = -1;  // tensor ids (res: residual added before ReLU)
+  int kh = 1, kw = 1, stride = 1, pad_h = 0, pad_w = 0;
+  bool relu = false;
+  // Keras weight arrays (indices into Net::warr; -1 = absent)
+  int w_kernel = -1, w_bias = -1, w_gamma = -1, w_beta = -1, w_mean = -1, w_var = -1;
+  float eps = 0.f;
+  // packed weights
+  int cin = 0, cout = 0, cin_pad = 0;
+  int64_t wpack_off = 0;  // bytes into the weights buffer
+  int64_t bias_off = 0;   // bytes into the weights buffer (fp32[cout])
+};
+
+struct Net {
+  int model = 0;
+  int input_size = 0;  // S
+  int mode = 0;        // 0 caffe, 1 tf
+  std::vector<WeightArr> warr;
+  int64_t total_floats = 0;
+  std::vector<Tensor> tensors;
+  std::vector<Buf> bufs;
+  std::vector<Op> ops;
+  int input_tensor = -1;
+  int pooled_tensor = -1;  // GAP output (fp32, outside the arena)
+  int fc_kernel = -1, fc_bias = -1;
+  int64_t fc_w_off = 0, fc_b_off = 0;  // bytes into the weights buffer (fp32)
+  int64_t arena_elems = 0;             // per image
+  int64_t weights_bytes = 0;
+  int64_t conv_macs = 0;               // per image
+};
+
+// Builds the graph.  keep_all: every tensor gets its own storage (parity taps).
+// wbytes: bytes per packed conv weight element (2 = bf16, 4 = fp32 check mode).
+// tc_pad: pad Cin of tensor-core-eligible convs to a multiple of 64.
+bool build_net(int model, bool keep_all, int wbytes, bool tc_pad, Net* net, std::string* err);
+
+// Only the weight-array list (cheap; for dml_model_* queries).
+bool build_weight_spec(int model, Net* net, std::string* err);
+
+}  // namespace dml

@@ -1,0 +1,398 @@
+// kernels.cu -- the HBM-bound kernels of the predict path and the CUDA-core
+// convolution used by the fp32 check mode.  sm_100a.
+//
+//  K1 preprocess : load_img NEAREST resize + img_to_array + preprocess_input
+//                  (/root/reference/models.py:34-38, :59-63)
+//  K4 maxpool / K5 avgpool / K6 global average pool / K7 dense+softmax+top-5:
+//                  pieces of modelObj.predict and decode_predictions
+//                  (/root/reference/models.py:40-42, :65-67)
+#include "kernels.h"
+
+#include <cuda_bf16.h>
+
+namespace dml {
+namespace {
+
+__device__ __forceinline__ float to_f(float v) { return v; }
+__device__ __forceinline__ float to_f(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// ---------------------------------------------------------------------------
+// K1: each thread produces 8 consecutive output elements (16 B of bf16).
+// ---------------------------------------------------------------------------
+template <typename TO>
+__global__ void __launch_bounds__(256) preprocess_kernel(PreParams p, const float* __restrict__ lut_g, int caffe) {
+  __shared__ float lut[768];
+  for (int i = threadIdx.x; i < 768; i += blockDim.x) lut[i] = lut_g[i];
+  __syncthreads();
+  const int S = p.S;
+  const int64_t per_img = (int64_t)S * S * 3;
+  const int64_t total = per_img * p.n;
+  int64_t e0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (e0 >= total) return;
+  int img = (int)(e0 / per_img);
+  int rem = (int)(e0 - (int64_t)img * per_img);
+  int pix = rem / 3;
+  int ch = rem - pix * 3;
+  int y = pix / S;
+  int x = pix - y * S;
+
+  const uint8_t* src = p.pixels + p.img_off[img];
+  int W = p.hw[2 * img + 1];
+  int sy = p.ytab[img * S + y];
+  int sx = p.xtab[img * S + x];
+  TO vals[8];
+  int cnt = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    if (e0 + i < total) {
+      int sc = caffe ? 2 - ch : ch;
+      uint8_t v = src[((int64_t)sy * W + sx) * 3 + sc];
+      vals[i] = from_f<TO>(lut[ch * 256 + v]);
+      cnt = i + 1;
+      if (++ch == 3) {
+        ch = 0;
+        if (++x == S) {
+          x = 0;
+          if (++y == S) {
+            y = 0;
+            ++img;
+            if (img < p.n) {
+              src = p.pixels + p.img_off[img];
+              W = p.hw[2 * img + 1];
+            }
+          }
+          if (img < p.n) sy = p.ytab[img * S + y];
+        }
+        if (img < p.n) sx = p.xtab[img * S + x];
+      }
+    } else {
+      vals[i] = from_f<TO>(0.f);
+    }
+  }
+  TO* out = reinterpret_cast<TO*>(p.out) + e0;
+  if (cnt == 8) {
+    if (sizeof(TO) == 2) {
+      *reinterpret_cast<uint4*>(out) = *reinterpret_cast<uint4*>(vals);
+    } else {
+      reinterpret_cast<uint4*>(out)[0] = reinterpret_cast<uint4*>(vals)[0];
+      reinterpret_cast<uint4*>(out)[1] = reinterpret_cast<uint4*>(vals)[1];
+    }
+  } else {
+    for (int i = 0; i < cnt; ++i) out[i] = vals[i];
+  }
+}
+
+// ---------------------------------------------------------------------------
+// CUDA-core direct convolution: 64 pixels x 64 output channels per block,
+// 4x4 outputs per thread, K = taps*Cin walked in chunks of 16.
+// ---------------------------------------------------------------------------
+template <typename TA, typename TW>
+__global__ void __launch_bounds__(256) conv_naive_kernel(ConvParams p) {
+  __shared__ float As[16][65];
+  __shared__ float Bs[16][65];
+  const TA* __restrict__ in = reinterpret_cast<const TA*>(p.in);
+  const TW* __restrict__ w = reinterpret_cast<const TW*>(p.w);
+  const int tid = threadIdx.x;
+  const int64_t M = (int64_t)p.n * p.ho * p.wo;
+  const int K = p.kh * p.kw * p.cin;
+  const int64_t m0 = (int64_t)blockIdx.x * 64;
+  const int n0 = blockIdx.y * 64;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int lp = tid >> 2, lk = (tid & 3) * 4;
+
+  // pixel this thread loads for the A tile
+  const int64_t lm = m0 + lp;
+  const bool lm_ok = lm < M;
+  int ln = 0, lho = 0, lwo = 0;
+  if (lm_ok) {
+    ln = (int)(lm / (p.ho * p.wo));
+    int r = (int)(lm - (int64_t)ln * p.ho * p.wo);
+    lho = r / p.wo;
+    lwo = r - lho * p.wo;
+  }
+  const int hbase = lho * p.stride - p.pad_h, wbase = lwo * p.stride - p.pad_w;
+  const int lco = n0 + lp;
+  const int64_t wrow = (int64_t)lco * p.kh * p.kw * p.cin_pad;
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = 0; k0 < K; k0 += 16) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      int k = k0 + lk + e;
+      float av = 0.f, bv = 0.f;
+      if (k < K) {
+        int tap = k / p.cin;
+        int c = k - tap * p.cin;
+        int r = tap / p.kw;
+        int s = tap - r * p.kw;
+        int hi = hbase + r, wi = wbase + s;
+        if (lm_ok && hi >= 0 && hi < p.hi && wi >= 0 && wi < p.wi)
+          av = to_f(in[(((int64_t)ln * p.hi + hi) * p.wi + wi) * p.in_pitch + c]);
+        if (lco < p.cout) bv = to_f(w[wrow + (int64_t)tap * p.cin_pad + c]);
+      }
+      As[lk + e][lp] = av;
+      Bs[lk + e][lp] = bv;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = As[kk][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = Bs[kk][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+
+  TA* out = reinterpret_cast<TA*>(p.out);
+  const TA* res = reinterpret_cast<const TA*>(p.res);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    int64_t m = m0 + ty * 4 + i;
+    if (m >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int co = n0 + tx * 4 + j;
+      if (co >= p.cout) continue;
+      float v = acc[i][j] + p.bias[co];
+      if (res) v += to_f(res[m * p.res_pitch + co]);
+      if (p.relu) v = fmaxf(v, 0.f);
+      out[m * p.out_pitch + co] = from_f<TA>(v);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// K4 / K5 pools: one thread per (output pixel, 8-channel group) for bf16,
+// (output pixel, 4-channel group) for fp32 -- 16-byte accesses either way.
+// ---------------------------------------------------------------------------
+template <typename T> struct Vec16;
+template <> struct Vec16<float> { static constexpr int N = 4; };
+template <> struct Vec16<__nv_bfloat16> { static constexpr int N = 8; };
+
+template <typename T, bool AVG>
+__global__ void __launch_bounds__(256) pool_kernel(PoolParams p) {
+  constexpr int V = Vec16<T>::N;
+  const int cg = p.c / V;
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t total = (int64_t)p.n * p.ho * p.wo * cg;
+  if (idx >= total) return;
+  int g = (int)(idx % cg);
+  int64_t pix = idx / cg;
+  int wo = (int)(pix % p.wo);
+  int64_t t = pix / p.wo;
+  int ho = (int)(t % p.ho);
+  int n = (int)(t / p.ho);
+  const T* in = reinterpret_cast<const T*>(p.in);
+  float acc[V];
+  // max-pool: Keras pads with ZEROS (ZeroPadding2D) where pad > 0, so an
+  // out-of-bounds tap contributes 0, not -inf.
+#pragma unroll
+  for (int i = 0; i < V; ++i) acc[i] = AVG ? 0.f : -INFINITY;
+  int valid = 0;
+  for (int r = 0; r < p.k; ++r) {
+    int hi = ho * p.stride - p.pad + r;
+    for (int s = 0; s < p.k; ++s) {
+      int wi = wo * p.stride - p.pad + s;
+      bool ok = hi >= 0 && hi < p.hi && wi >= 0 && wi < p.wi;
+      if (ok) {
+        ++valid;
+        uint4 raw = *reinterpret_cast<const uint4*>(in + (((int64_t)n * p.hi + hi) * p.wi + wi) * p.in_pitch + g * V);
+        const T* v = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+          float f = to_f(v[i]);
+          acc[i] = AVG ? acc[i] + f : fmaxf(acc[i], f);
+        }
+      } else if (!AVG) {
+#pragma unroll
+        for (int i = 0; i < V; ++i) acc[i] = fmaxf(acc[i], 0.f);
+      }
+    }
+  }
+  T o[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) o[i] = from_f<T>(AVG ? acc[i] / (float)valid : acc[i]);
+  T* out = reinterpret_cast<T*>(p.out) + (((int64_t)n * p.ho + ho) * p.wo + wo) * p.out_pitch + g * V;
+  *reinterpret_cast<uint4*>(out) = *reinterpret_cast<uint4*>(o);
+}
+
+// K6: one thread per (image, V-channel group), walks the HxW pixels.
+template <typename T>
+__global__ void __launch_bounds__(256) gap_kernel(const T* __restrict__ in, float* __restrict__ out, int n, int hw, int c,
+                                                  int in_pitch) {
+  constexpr int V = Vec16<T>::N;
+  const int cg = c / V;
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n * cg) return;
+  int g = idx % cg, img = idx / cg;
+  float acc[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) acc[i] = 0.f;
+  const T* base = in + (int64_t)img * hw * in_pitch + g * V;
+  for (int px = 0; px < hw; ++px) {
+    uint4 raw = *reinterpret_cast<const uint4*>(base + (int64_t)px * in_pitch);
+    const T* v = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+    for (int i = 0; i < V; ++i) acc[i] += to_f(v[i]);
+  }
+  float inv = 1.f / (float)hw;
+#pragma unroll
+  for (int i = 0; i < V; ++i) out[(int64_t)img * c + g * V + i] = acc[i] * inv;
+}
+
+// K7a: logits[img][j] = pooled[img] . W[:, j] + b[j].  Block = 8 images x 128
+// columns; pooled rows staged in shared memory, W read once per 8 images.
+constexpr int FC_IMGS = 8;
+constexpr int FC_COLS = 128;
+__global__ void __launch_bounds__(FC_COLS) fc_kernel(const float* __restrict__ pooled, const float* __restrict__ w,
+                                                     const float* __restrict__ b, float* __restrict__ logits, int n,
+                                                     int cin) {
+  extern __shared__ float xs[];  // FC_IMGS x cin
+  const int img0 = blockIdx.x * FC_IMGS;
+  const int col = blockIdx.y * FC_COLS + threadIdx.x;
+  for (int i = threadIdx.x; i < FC_IMGS * cin; i += FC_COLS) {
+    int im = img0 + i / cin;
+    xs[i] = im < n ? pooled[(int64_t)im * cin + (i % cin)] : 0.f;
+  }
+  __syncthreads();
+  if (col >= 1000) return;
+  float acc[FC_IMGS];
+#pragma unroll
+  for (int i = 0; i < FC_IMGS; ++i) acc[i] = 0.f;
+  for (int k = 0; k < cin; ++k) {
+    float wv = w[(int64_t)k * 1000 + col];
+#pragma unroll
+    for (int i = 0; i < FC_IMGS; ++i) acc[i] = fmaf(xs[i * cin + k], wv, acc[i]);
+  }
+  float bv = b[col];
+#pragma unroll
+  for (int i = 0; i < FC_IMGS; ++i)
+    if (img0 + i < n) logits[(int64_t)(img0 + i) * 1000 + col] = acc[i] + bv;
+}
+
+// K7b: softmax over 1000 logits + top-5 (descending prob; ties -> larger index).
+__global__ void __launch_bounds__(256) softmax_top5_kernel(const float* __restrict__ logits, float* __restrict__ probs,
+                                                           int32_t* __restrict__ top_idx, float* __restrict__ top_prob,
+                                                           int n) {
+  __shared__ float sp[1000];
+  __shared__ float red[8];
+  __shared__ int redi[8];
+  const int img = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const float* lg = logits + (int64_t)img * 1000;
+  float mx = -INFINITY;
+  for (int j = tid; j < 1000; j += 256) mx = fmaxf(mx, lg[j]);
+  for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0) red[wid] = mx;
+  __syncthreads();
+  mx = red[0];
+  for (int i = 1; i < 8; ++i) mx = fmaxf(mx, red[i]);
+  __syncthreads();
+  float sum = 0.f;
+  for (int j = tid; j < 1000; j += 256) {
+    float e = expf(lg[j] - mx);
+    sp[j] = e;
+    sum += e;
+  }
+  for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) red[wid] = sum;
+  __syncthreads();
+  sum = 0.f;
+  for (int i = 0; i < 8; ++i) sum += red[i];
+  __syncthreads();
+  for (int j = tid; j < 1000; j += 256) {
+    float pr = sp[j] / sum;
+    sp[j] = pr;
+    if (probs) probs[(int64_t)img * 1000 + j] = pr;
+  }
+  __syncthreads();
+  for (int t = 0; t < 5; ++t) {
+    float bv = -1.f;
+    int bi = -1;
+    for (int j = tid; j < 1000; j += 256) {
+      float v = sp[j];
+      if (v > bv || (v == bv && j > bi)) { bv = v; bi = j; }
+    }
+    for (int o = 16; o; o >>= 1) {
+      float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > bv || (ov == bv && oi > bi)) { bv = ov; bi = oi; }
+    }
+    if (lane == 0) { red[wid] = bv; redi[wid] = bi; }
+    __syncthreads();
+    if (tid == 0) {
+      for (int i = 1; i < 8; ++i)
+        if (red[i] > bv || (red[i] == bv && redi[i] > bi)) { bv = red[i]; bi = redi[i]; }
+      top_idx[img * 5 + t] = bi;
+      top_prob[img * 5 + t] = bv;
+      sp[bi] = -2.f;  // remove from the next rounds
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace
+
+void launch_preprocess(const PreParams& p, const float* d_lut, bool fp32_out, cudaStream_t s) {
+  int64_t total = (int64_t)p.n * p.S * p.S * 3;
+  int64_t threads = (total + 7) / 8;
+  unsigned blocks = (unsigned)((threads + 255) / 256);
+  if (fp32_out) preprocess_kernel<float><<<blocks, 256, 0, s>>>(p, d_lut, p.caffe);
+  else preprocess_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(p, d_lut, p.caffe);
+}
+
+void launch_conv_naive(const ConvParams& p, bool fp32_act, cudaStream_t s) {
+  int64_t M = (int64_t)p.n * p.ho * p.wo;
+  dim3 grid((unsigned)((M + 63) / 64), (unsigned)((p.cout + 63) / 64));
+  if (fp32_act) conv_naive_kernel<float, float><<<grid, 256, 0, s>>>(p);
+  else conv_naive_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 256, 0, s>>>(p);
+}
+
+template <bool AVG>
+static void launch_pool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
+  int V = fp32_act ? 4 : 8;
+  int64_t total = (int64_t)p.n * p.ho * p.wo * (p.c / V);
+  unsigned blocks = (unsigned)((total + 255) / 256);
+  if (fp32_act) pool_kernel<float, AVG><<<blocks, 256, 0, s>>>(p);
+  else pool_kernel<__nv_bfloat16, AVG><<<blocks, 256, 0, s>>>(p);
+}
+void launch_maxpool(const PoolParams& p, bool fp32_act, cudaStream_t s) { launch_pool<false>(p, fp32_act, s); }
+void launch_avgpool(const PoolParams& p, bool fp32_act, cudaStream_t s) { launch_pool<true>(p, fp32_act, s); }
+
+void launch_gap(const void* in, float* out, int n, int hw, int c, int in_pitch, bool fp32_act, cudaStream_t s) {
+  int V = fp32_act ? 4 : 8;
+  int total = n * (c / V);
+  unsigned blocks = (unsigned)((total + 255) / 256);
+  if (fp32_act) gap_kernel<float><<<blocks, 256, 0, s>>>(reinterpret_cast<const float*>(in), out, n, hw, c, in_pitch);
+  else gap_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(in), out, n, hw, c, in_pitch);
+}
+
+void init_kernels() {
+  cudaFuncSetAttribute(fc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+}
+
+void launch_fc(const float* pooled, const float* w, const float* b, float* logits, int n, int cin, cudaStream_t s) {
+  dim3 grid((unsigned)((n + FC_IMGS - 1) / FC_IMGS), (1000 + FC_COLS - 1) / FC_COLS);
+  size_t smem = (size_t)FC_IMGS * cin * sizeof(float);
+  fc_kernel<<<grid, FC_COLS, smem, s>>>(pooled, w, b, logits, n, cin);
+}
+
+void launch_softmax_top5(const float* logits, float* probs, int32_t* top_idx, float* top_prob, int n, cudaStream_t s) {
+  softmax_top5_kernel<<<n, 256, 0, s>>>(logits, probs, top_idx, top_prob, n);
+}
+
+}  // namespace dml

@@ -1,0 +1,60 @@
+// kernels.h -- launchers of the hand-written sm_100a kernels (internal).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace dml {
+
+struct ConvParams {
+  const void* in;     // NHWC activations, pointer already offset to the view's first channel
+  const void* w;      // packed weights [cout][kh*kw][cin_pad]
+  const float* bias;  // folded bias [cout]
+  const void* res;    // residual (same dtype as out) or nullptr
+  void* out;
+  int n, hi, wi, cin, in_pitch;
+  int ho, wo, cout, out_pitch, res_pitch;
+  int kh, kw, stride, pad_h, pad_w, cin_pad;
+  int relu;
+};
+
+struct PoolParams {
+  const void* in;
+  void* out;
+  int n, hi, wi, c, in_pitch;
+  int ho, wo, out_pitch;
+  int k, stride, pad;
+};
+
+struct PreParams {
+  const uint8_t* pixels;
+  const int64_t* img_off;
+  const int32_t* hw;    // (H, W) per image
+  const int32_t* xtab;  // n x S
+  const int32_t* ytab;  // n x S
+  void* out;            // n x S x S x 3
+  int n, S;
+  int caffe;            // 1: output channel c reads source channel 2-c (RGB->BGR)
+};
+
+// K1: NEAREST resize (host-computed index tables) + preprocess LUT; bf16 or fp32 out.
+void launch_preprocess(const PreParams& p, const float* d_lut, bool fp32_out, cudaStream_t s);
+
+// CUDA-core direct convolution (check mode, debug twin, C=3 stems).
+void launch_conv_naive(const ConvParams& p, bool fp32_act, cudaStream_t s);
+
+// K4 / K5: 3x3 max-pool (zero padding participates, as Keras' ZeroPadding2D does)
+// and 3x3 s1 'same' average pool dividing by the in-bounds tap count.
+void launch_maxpool(const PoolParams& p, bool fp32_act, cudaStream_t s);
+void launch_avgpool(const PoolParams& p, bool fp32_act, cudaStream_t s);
+
+// K6: global average pool -> fp32 [n][c]
+void launch_gap(const void* in, float* out, int n, int hw, int c, int in_pitch, bool fp32_act, cudaStream_t s);
+
+// K7: Dense(1000) -> logits scratch; softmax + top-5.
+void launch_fc(const float* pooled, const float* w, const float* b, float* logits, int n, int cin, cudaStream_t s);
+// Per-device one-time kernel attribute set-up (call with the device current).
+void init_kernels();
+
+void launch_softmax_top5(const float* logits, float* probs, int32_t* top_idx, float* top_prob, int n, cudaStream_t s);
+
+}  // namespace dml

@@ -1,0 +1,204 @@
+"""Engine: one resident model per (process, GPU), driven through the C ABI.
+
+Replaces the per-task ``ResNet50(weights=...)`` / ``InceptionV3(weights=...)`` +
+``predict`` of /root/reference/models.py:25-26, :40, :50-51, :65.  PyTorch is used
+for device/pinned allocations and the CUDA stream only; every kernel is ours and
+runs through libdml_b200.so.  No CPU fallback: without a GPU this raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib, frontend, keras_weights
+
+
+def _torch():
+    import torch
+    return torch
+
+
+class Engine:
+    def __init__(self, model_name: str, device: int = 0, max_batch: int = 256, micro_batch: int = 0,
+                 fp32_check: bool = False, tensor_cores: bool = True, keep_all: bool = False,
+                 weights=None, load: bool = True):
+        torch = _torch()
+        if not torch.cuda.is_available():
+            raise _lib.DmlError("no CUDA device: the dml_b200 engine has no CPU fallback")
+        self.l = _lib.lib()
+        self.model_name = model_name
+        self.device = device
+        self.max_batch = max_batch
+        self.size, self.mode = _lib.model_info(model_name)
+        flags = (_lib.FLAG_FP32_CHECK if fp32_check else 0) | (0 if tensor_cores else _lib.FLAG_NO_TENSOR_CORE) | \
+                (_lib.FLAG_KEEP_ALL if keep_all else 0)
+        self.fp32 = fp32_check
+        self.h = C.c_void_p()
+        torch.cuda.set_device(device)
+        _lib.check(self.l.dml_create(device, _lib.model_id(model_name), max_batch, micro_batch, flags, C.byref(self.h)))
+        ws, wt = C.c_size_t(), C.c_size_t()
+        _lib.check(self.l.dml_workspace_bytes(self.h, C.byref(ws)))
+        _lib.check(self.l.dml_weights_bytes(self.h, C.byref(wt)))
+        dev = torch.device("cuda", device)
+        self.stream = torch.cuda.Stream(device=dev)
+        self.workspace = torch.empty(ws.value + 256, dtype=torch.uint8, device=dev)
+        self.weights = torch.empty(wt.value + 256, dtype=torch.uint8, device=dev)
+        self._ws_ptr = (self.workspace.data_ptr() + 255) // 256 * 256
+        self._wt_ptr = (self.weights.data_ptr() + 255) // 256 * 256
+        self.weights_bytes = wt.value
+        _lib.check(self.l.dml_bind_weights(self.h, self._wt_ptr, wt.value))
+        _lib.check(self.l.dml_bind_workspace(self.h, self._ws_ptr, ws.value))
+        # device-side inputs/outputs, sized for max_batch
+        S = self.size
+        self.max_pixels = max_batch * 300 * 300 * 3
+        self.d_pixels = torch.empty(self.max_pixels + 16, dtype=torch.uint8, device=dev)
+        self.d_off = torch.empty(max_batch, dtype=torch.int64, device=dev)
+        self.d_hw = torch.empty((max_batch, 2), dtype=torch.int32, device=dev)
+        self.d_xtab = torch.empty((max_batch, S), dtype=torch.int32, device=dev)
+        self.d_ytab = torch.empty((max_batch, S), dtype=torch.int32, device=dev)
+        self.d_probs = torch.empty((max_batch, 1000), dtype=torch.float32, device=dev)
+        self.d_idx = torch.empty((max_batch, 5), dtype=torch.int32, device=dev)
+        self.d_prob = torch.empty((max_batch, 5), dtype=torch.float32, device=dev)
+        self.h_idx = torch.empty((max_batch, 5), dtype=torch.int32).pin_memory()
+        self.h_prob = torch.empty((max_batch, 5), dtype=torch.float32).pin_memory()
+        if load:
+            self.load_weights(weights)
+
+    # -- weights ---------------------------------------------------------
+    def load_weights(self, weights=None):
+        """weights: flat fp32 blob, list of arrays in blob order, or None (file/env or fixed-seed default)."""
+        if weights is None:
+            blob = keras_weights.load_blob(self.model_name)
+        elif isinstance(weights, np.ndarray) and weights.ndim == 1:
+            blob = np.ascontiguousarray(weights, dtype=np.float32)
+        else:
+            blob = keras_weights.to_blob(weights)
+        _lib.check(self.l.dml_load_weights(self.h, blob.ctypes.data, blob.size))
+
+    def packed_weights(self):
+        """The packed device weights as a torch uint8 view (for an NCCL broadcast)."""
+        off = self._wt_ptr - self.weights.data_ptr()
+        return self.weights[off:off + self.weights_bytes]
+
+    def weights_ready(self):
+        _lib.check(self.l.dml_weights_ready(self.h))
+
+    # -- hot path --------------------------------------------------------
+    def upload(self, hb: frontend.HostBatch):
+        """Host->device copy of one HostBatch on the engine stream."""
+        torch = _torch()
+        n = hb.n
+        if n > self.max_batch:
+            raise _lib.DmlError(f"batch of {n} exceeds max_batch {self.max_batch}")
+        if hb.pixels.size > self.d_pixels.numel():
+            raise _lib.DmlError("pixel blob larger than the device staging buffer")
+        with torch.cuda.stream(self.stream):
+            self.d_pixels[:hb.pixels.size].copy_(torch.from_numpy(hb.pixels), non_blocking=True)
+            self.d_off[:n].copy_(torch.from_numpy(hb.img_off), non_blocking=True)
+            self.d_hw[:n].copy_(torch.from_numpy(hb.hw), non_blocking=True)
+            self.d_xtab[:n].copy_(torch.from_numpy(hb.xtab), non_blocking=True)
+            self.d_ytab[:n].copy_(torch.from_numpy(hb.ytab), non_blocking=True)
+
+    def preprocess(self, n: int):
+        _lib.check(self.l.dml_preprocess(self.h, self.d_pixels.data_ptr(), self.d_off.data_ptr(), self.d_hw.data_ptr(),
+                                         self.d_xtab.data_ptr(), self.d_ytab.data_ptr(), n, self.stream.cuda_stream))
+
+    def forward(self, n: int, want_probs: bool = True):
+        _lib.check(self.l.dml_forward(self.h, n, self.d_probs.data_ptr() if want_probs else None,
+                                      self.d_idx.data_ptr(), self.d_prob.data_ptr(), self.stream.cuda_stream))
+
+    def infer_device(self, n: int, want_probs: bool = False):
+        """dml_infer on what upload() put on the device; results stay on the device."""
+        _lib.check(self.l.dml_infer(self.h, self.d_pixels.data_ptr(), self.d_off.data_ptr(), self.d_hw.data_ptr(),
+                                    self.d_xtab.data_ptr(), self.d_ytab.data_ptr(), n,
+                                    self.d_probs.data_ptr() if want_probs else None, self.d_idx.data_ptr(),
+                                    self.d_prob.data_ptr(), self.stream.cuda_stream))
+
+    def predict_images(self, images, want_probs: bool = False):
+        """uint8 HxWx3 arrays -> (top5_idx [n,5] int32, top5_prob [n,5] fp32[, probs [n,1000]])."""
+        torch = _torch()
+        idx_out, prob_out, probs_out = [], [], []
+        for i in range(0, len(images), self.max_batch):
+            chunk = images[i:i + self.max_batch]
+            hb = frontend.HostBatch(chunk, self.size)
+            self.upload(hb)
+            self.infer_device(hb.n, want_probs)
+            with torch.cuda.stream(self.stream):
+                self.h_idx[:hb.n].copy_(self.d_idx[:hb.n], non_blocking=True)
+                self.h_prob[:hb.n].copy_(self.d_prob[:hb.n], non_blocking=True)
+            self.stream.synchronize()
+            idx_out.append(self.h_idx[:hb.n].numpy().copy())
+            prob_out.append(self.h_prob[:hb.n].numpy().copy())
+            if want_probs:
+                probs_out.append(self.d_probs[:hb.n].cpu().numpy())
+        if not idx_out:
+            e = (np.zeros((0, 5), np.int32), np.zeros((0, 5), np.float32))
+            return e + ((np.zeros((0, 1000), np.float32),) if want_probs else ())
+        r = (np.concatenate(idx_out), np.concatenate(prob_out))
+        return r + ((np.concatenate(probs_out),) if want_probs else ())
+
+    # -- inspection ------------------------------------------------------
+    def input_tensor(self, n: int):
+        torch = _torch()
+        p, eb = C.c_void_p(), C.c_int()
+        _lib.check(self.l.dml_input_tensor(self.h, C.byref(p), C.byref(eb)))
+        off = p.value - self.workspace.data_ptr()
+        nbytes = n * self.size * self.size * 3 * eb.value
+        raw = self.workspace[off:off + nbytes]
+        dt = torch.float32 if eb.value == 4 else torch.bfloat16
+        return raw.view(dt).view(n, self.size, self.size, 3)
+
+    def logits(self, n: int):
+        torch = _torch()
+        p = C.c_void_p()
+        _lib.check(self.l.dml_logits(self.h, C.byref(p)))
+        off = p.value - self.workspace.data_ptr()
+        return self.workspace[off:off + n * 4000].view(torch.float32).view(n, 1000)
+
+    def tensors(self):
+        """{name: (index, h, w, c, c_pitch, elem_bytes, dev_ptr)}"""
+        n = C.c_int()
+        _lib.check(self.l.dml_num_tensors(self.h, C.byref(n)))
+        out = {}
+        buf = C.create_string_buffer(128)
+        for i in range(n.value):
+            h, w, c, cp, eb, keep = (C.c_int() for _ in range(6))
+            p = C.c_void_p()
+            _lib.check(self.l.dml_tensor_info(self.h, i, buf, 128, C.byref(h), C.byref(w), C.byref(c), C.byref(p),
+                                              C.byref(cp), C.byref(eb), C.byref(keep)))
+            out[buf.value.decode()] = (i, h.value, w.value, c.value, cp.value, eb.value, p.value)
+        return out
+
+    def read_tensor(self, name: str, n: int):
+        """Copy a tensor of the current micro-batch to the host as fp32 NHWC (keep_all engines)."""
+        torch = _torch()
+        _, h, w, c, cp, eb, ptr = self.tensors()[name]
+        off = ptr - self.workspace.data_ptr()
+        nbytes = ((n * h * w - 1) * cp + c) * eb
+        raw = self.workspace[off:off + nbytes + (-nbytes) % eb]
+        dt = torch.float32 if eb == 4 else torch.bfloat16
+        flat = raw.view(dt)
+        full = torch.zeros(n * h * w * cp, dtype=dt, device=flat.device)
+        full[:flat.numel()] = flat
+        return full.view(n, h, w, cp)[..., :c].float().cpu().numpy()
+
+    def launch_count(self) -> int:
+        v = C.c_int64()
+        _lib.check(self.l.dml_launch_count(self.h, C.byref(v)))
+        return v.value
+
+    def sync(self):
+        self.stream.synchronize()
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.sync()
+            self.l.dml_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

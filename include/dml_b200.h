@@ -1,0 +1,153 @@
+/*
+ * dml_b200.h -- C ABI of libdml_b200.so, the B200 (sm_100a) batch-inference
+ * engine behind the reference's models.py predict path.
+ *
+ * Every entry point replaces a piece of what /root/reference/models.py does
+ * through TensorFlow/Keras; the citation on each declaration names the
+ * reference line(s) it stands in for.  Plain pointers and sizes only; no torch
+ * types.  All functions return 0 on success and a negative DML_E* code on
+ * failure; dml_last_error() gives the message (thread-local).
+ *
+ * Ownership: the caller (Python + torch in this repo) allocates every device
+ * buffer and passes raw device pointers; the library allocates no device
+ * memory in any of these entry points.  Kernels are enqueued on the stream the
+ * caller passes (a cudaStream_t cast to void*; NULL = default stream) and the
+ * calls return without waiting, except dml_sync and dml_load_weights.
+ */
+#ifndef DML_B200_H_
+#define DML_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct dml_engine dml_engine;
+
+enum {
+  DML_OK = 0,
+  DML_EINVAL = -1,   /* bad argument */
+  DML_ESTATE = -2,   /* call order: workspace/weights not bound or loaded */
+  DML_ECUDA = -3,    /* a CUDA runtime/driver call failed */
+  DML_ESIZE = -4     /* size beyond a stated limit */
+};
+
+enum { DML_MODEL_RESNET50 = 0, DML_MODEL_INCEPTIONV3 = 1 };
+
+/* dml_create flags */
+enum {
+  DML_FLAG_FP32_CHECK = 1,   /* fp32 activations+weights, CUDA-core convs (the "fp32-accumulate check mode") */
+  DML_FLAG_NO_TENSOR_CORE = 2, /* bf16 storage but CUDA-core convs (debug twin of the tcgen05 path) */
+  DML_FLAG_KEEP_ALL = 4        /* no activation-buffer reuse: every tensor stays readable (parity taps) */
+};
+
+#define DML_NUM_CLASSES 1000
+#define DML_TOP 5
+
+/* ---- model description (no GPU needed) ---------------------------------- */
+
+/* Input side S (224 / 299) and preprocess mode (0 = caffe, 1 = tf) of a model:
+ * the target_size / preprocess_input pair at models.py:34,38 and :59,63. */
+int dml_model_info(int model, int* input_size, int* preprocess_mode);
+
+/* Number of weight arrays and total fp32 element count of the Keras-layout
+ * blob (ResNet50(...) / InceptionV3(...) construction, models.py:26, :51). */
+int dml_model_num_weights(int model, int* num_arrays, int64_t* total_floats);
+
+/* Name and shape of weight array i in blob order (layer creation order, each
+ * layer in Keras get_weights() order).  shape[4], rank <= 4. */
+int dml_model_weight_info(int model, int i, char* name, int name_cap, int64_t shape[4], int* rank);
+
+/* The three 256-entry fp32 look-up tables preprocess_input reduces to for uint8
+ * input: out[c*256 + v] is the value of OUTPUT channel c for source byte v
+ * (models.py:38 tf mode, :63 caffe mode).  For caffe, output channel c reads
+ * source channel 2-c. */
+int dml_preprocess_lut(int model, float out[768]);
+
+/* ---- engine lifetime ------------------------------------------------------ */
+
+/* One engine per (process, device, model); replaces the per-task model build
+ * at models.py:25-26 / :50-51.  max_batch = largest n a later call may pass;
+ * micro_batch = images pushed through the layer stack together (0 = default). */
+int dml_create(int device, int model, int max_batch, int micro_batch, int flags, dml_engine** out);
+void dml_destroy(dml_engine* e);
+
+/* Sizes of the two device buffers the caller must allocate (256-byte aligned)
+ * and bind before any compute call. */
+int dml_workspace_bytes(dml_engine* e, size_t* bytes);
+int dml_weights_bytes(dml_engine* e, size_t* bytes);
+int dml_bind_workspace(dml_engine* e, void* dev_ptr, size_t bytes);
+int dml_bind_weights(dml_engine* e, void* dev_ptr, size_t bytes);
+
+/* Keras-layout fp32 host blob -> fold BN (+bias) into each conv -> pack
+ * (bf16 K-major, or fp32 in check mode) -> copy into the bound weights buffer.
+ * Stands in for ResNet50(weights=...)/InceptionV3(weights=...) at models.py:26,:51.
+ * Synchronous. */
+int dml_load_weights(dml_engine* e, const float* host_blob, size_t num_floats);
+
+/* Marks the bound weights buffer as already holding packed weights (after the
+ * caller replicated another rank's buffer, e.g. with an NCCL broadcast). */
+int dml_weights_ready(dml_engine* e);
+
+/* ---- the hot path --------------------------------------------------------- */
+
+/* load_img's NEAREST resize + img_to_array + preprocess_input for n images
+ * (models.py:34-38, :59-63).  d_pixels: concatenated uint8 RGB HxWx3 images;
+ * d_img_off[n]: byte offset of each image; d_hw[2n]: (H, W) per image;
+ * d_xtab[n*S], d_ytab[n*S]: source column/row per output column/row (Pillow's
+ * running-sum rule, computed on the host).  Writes the engine's input tensor. */
+int dml_preprocess(dml_engine* e, const uint8_t* d_pixels, const int64_t* d_img_off, const int32_t* d_hw,
+                   const int32_t* d_xtab, const int32_t* d_ytab, int n, void* stream);
+
+/* modelObj.predict + decode_predictions(top=5) on the n preprocessed images
+ * (models.py:40-42, :65-67).  d_probs: n x 1000 softmax (may be NULL);
+ * d_top5_idx / d_top5_prob: n x 5, descending probability, ties -> larger
+ * class index first. */
+int dml_forward(dml_engine* e, int n, float* d_probs, int32_t* d_top5_idx, float* d_top5_prob, void* stream);
+
+/* dml_preprocess + dml_forward fused per micro-batch (the production path:
+ * the whole per-file loop body of models.py:30-44 / :55-69 for n files). */
+int dml_infer(dml_engine* e, const uint8_t* d_pixels, const int64_t* d_img_off, const int32_t* d_hw,
+              const int32_t* d_xtab, const int32_t* d_ytab, int n, float* d_probs, int32_t* d_top5_idx,
+              float* d_top5_prob, void* stream);
+
+/* ---- inspection (parity taps, counters) ----------------------------------- */
+
+/* Number of tensors in the engine's plan; tensor i's name, logical shape
+ * (h, w, c), and where it lives: device pointer of image 0 of the CURRENT
+ * micro-batch, channel pitch (elements) and element size in bytes.  Tensors
+ * are valid after dml_forward/dml_infer only if the engine was created with
+ * micro_batch >= n (buffers are reused between micro-batches). */
+int dml_num_tensors(dml_engine* e, int* n);
+int dml_tensor_info(dml_engine* e, int i, char* name, int name_cap, int* h, int* w, int* c, void** dev_ptr,
+                    int* c_pitch, int* elem_bytes, int* keep);
+
+/* The engine's preprocessed input tensor: n x S x S x 3 (bf16, or fp32 in check mode). */
+int dml_input_tensor(dml_engine* e, void** dev_ptr, int* elem_bytes);
+
+/* Logits (pre-softmax), n x 1000 fp32, valid after dml_forward / dml_infer. */
+int dml_logits(dml_engine* e, float** dev_ptr);
+
+/* Kernels launched by this engine since creation (all of them ours). */
+int dml_launch_count(dml_engine* e, int64_t* launches);
+
+/* One Conv2D + folded bias (+ residual) (+ ReLU) of predict (models.py:40, :65)
+ * over explicit device buffers: bf16 NHWC activations (channel pitches in
+ * elements), packed bf16 weights [cout][kh*kw][cin_pad], fp32 bias.
+ * impl 0 = CUDA-core kernel, 1 = tcgen05 kernel (tile_n / stages: 0 = default).
+ * The unit-test and tuning hook for the convolution kernels. */
+int dml_conv2d_bf16(int impl, const void* d_in, const void* d_w, const float* d_bias, const void* d_res, void* d_out,
+                    int n, int hi, int wi, int cin, int in_pitch, int cout, int out_pitch, int res_pitch, int kh,
+                    int kw, int stride, int pad_h, int pad_w, int cin_pad, int relu, int tile_n, int stages,
+                    void* stream);
+
+int dml_sync(dml_engine* e);
+const char* dml_last_error(void);
+const char* dml_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DML_B200_H_ */

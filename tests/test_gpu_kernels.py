@@ -1,0 +1,160 @@
+"""GPU parity of the individual kernels through the C ABI: K1 (bit-exact against
+Pillow + numpy), and the convolution kernels against a torch fp32 reference on
+bf16-rounded operands (the tcgen05 kernel additionally against the CUDA-core one)."""
+import ctypes as C
+import hashlib
+
+import numpy as np
+import pytest
+
+from conftest import pkg
+from oracle import frontend as ofe
+
+pytestmark = pytest.mark.gpu
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.fixture(scope="module")
+def engines():
+    E = pkg("engine").Engine
+    out = {}
+    for m in ("ResNet50", "InceptionV3"):
+        out[m, "fp32"] = E(m, max_batch=200, micro_batch=8, fp32_check=True, load=False)
+        out[m, "bf16"] = E(m, max_batch=200, micro_batch=8, load=False)
+    yield out
+    for e in out.values():
+        e.close()
+
+
+@pytest.mark.parametrize("model", ["ResNet50", "InceptionV3"])
+def test_preprocess_bit_exact_all_200(model, engines, images, jpeg_bytes, frontend_golden):
+    """K1 == load_img (Pillow NEAREST) + preprocess_input, bit for bit, on every bundled image."""
+    import torch
+    fe = pkg("frontend")
+    size, mode = ofe.MODEL_INPUT[model]
+    g = frontend_golden
+    for kind in ("fp32", "bf16"):
+        eng = engines[model, kind]
+        hb = fe.HostBatch(images, size)
+        eng.upload(hb)
+        eng.preprocess(hb.n)
+        eng.sync()
+        got = eng.input_tensor(hb.n)
+        if kind == "fp32":
+            got = got.cpu().numpy()
+            for i in range(hb.n):
+                assert sha(got[i]) == g[f"sha_pre_{size}_{mode}"][i], (model, i)
+        else:
+            # bf16 mode stores the round-to-nearest-even bf16 of the same fp32 value
+            for i in range(0, hb.n, 7):
+                want = ofe.load_and_preprocess(jpeg_bytes[str(g["names"][i])], model)
+                w16 = torch.from_numpy(want).to(torch.bfloat16)
+                assert torch.equal(got[i].cpu(), w16), (model, i)
+
+
+def test_preprocess_ragged_and_empty(engines):
+    fe = pkg("frontend")
+    eng = engines["InceptionV3", "fp32"]
+    rng = np.random.default_rng(1)
+    imgs = [rng.integers(0, 256, size=(h, w, 3), dtype=np.uint8) for h, w in [(1, 1), (299, 299), (300, 169), (114, 300), (7, 513)]]
+    hb = fe.HostBatch(imgs, 299)
+    eng.upload(hb)
+    eng.preprocess(hb.n)
+    eng.sync()
+    got = eng.input_tensor(hb.n).cpu().numpy()
+    for i, im in enumerate(imgs):
+        want = ofe.preprocess(ofe.resize_nearest_tables(im, 299), "tf")
+        assert np.array_equal(got[i].view(np.uint32), want.view(np.uint32)), i
+    eng.preprocess(0)  # n = 0 is a no-op, not an error
+
+
+def _conv_case(rng, n, hi, wi, cin, cout, kh, kw, stride, pad_h, pad_w, relu, with_res, in_extra=0, out_extra=0):
+    import torch
+    import torch.nn.functional as F
+    dev = torch.device("cuda")
+    in_pitch, cin_pad = cin + in_extra, (cin + 63) // 64 * 64
+    ho, wo = (hi + 2 * pad_h - kh) // stride + 1, (wi + 2 * pad_w - kw) // stride + 1
+    out_pitch = cout + out_extra
+    x = torch.from_numpy(rng.standard_normal((n, hi, wi, in_pitch)).astype(np.float32)).to(dev).bfloat16()
+    w = torch.from_numpy((rng.standard_normal((cout, kh, kw, cin)) / np.sqrt(kh * kw * cin)).astype(np.float32)).to(dev).bfloat16()
+    wp = torch.zeros((cout, kh * kw, cin_pad), dtype=torch.bfloat16, device=dev)
+    wp[:, :, :cin] = w.reshape(cout, kh * kw, cin)
+    bias = torch.from_numpy(rng.standard_normal(cout).astype(np.float32)).to(dev)
+    res = torch.from_numpy(rng.standard_normal((n, ho, wo, cout)).astype(np.float32)).to(dev).bfloat16() if with_res else None
+    ref = F.conv2d(x[..., :cin].float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), bias, stride=stride,
+                   padding=(pad_h, pad_w)).permute(0, 2, 3, 1)
+    if with_res:
+        ref = ref + res.float()
+    if relu:
+        ref = ref.relu()
+    return dict(x=x, wp=wp, bias=bias, res=res, ref=ref, geom=(n, hi, wi, cin, in_pitch, cout, out_pitch, cout if with_res else 0,
+                kh, kw, stride, pad_h, pad_w, cin_pad, int(relu)), ho=ho, wo=wo)
+
+
+def _run_conv(impl, case, tile_n=0, stages=0):
+    import torch
+    lib = pkg("_lib")
+    n, hi, wi, cin, in_pitch, cout, out_pitch = case["geom"][:7]
+    out = torch.full((n, case["ho"], case["wo"], out_pitch), 7.0, dtype=torch.bfloat16, device="cuda")
+    res = case["res"]
+    lib.check(lib.lib().dml_conv2d_bf16(impl, case["x"].data_ptr(), case["wp"].data_ptr(), case["bias"].data_ptr(),
+                                        res.data_ptr() if res is not None else None, out.data_ptr(), *case["geom"],
+                                        tile_n, stages, None))
+    torch.cuda.synchronize()
+    return out
+
+
+CONV_SHAPES = [
+    # n, hi, wi, cin, cout, kh, kw, stride, pad_h, pad_w, relu, res, in_extra, out_extra
+    (2, 56, 56, 64, 64, 1, 1, 1, 0, 0, True, False, 0, 0),
+    (2, 56, 56, 64, 256, 1, 1, 1, 0, 0, True, True, 0, 0),
+    (3, 56, 56, 256, 128, 1, 1, 2, 0, 0, True, False, 0, 0),
+    (2, 28, 28, 128, 128, 3, 3, 1, 1, 1, True, False, 0, 0),
+    (5, 7, 7, 512, 512, 3, 3, 1, 1, 1, True, False, 0, 0),
+    (3, 14, 14, 1024, 2048, 1, 1, 2, 0, 0, False, False, 0, 0),
+    (2, 35, 35, 48, 64, 5, 5, 1, 2, 2, True, False, 0, 32),      # ragged Cin, concat-slice store
+    (2, 35, 35, 288, 384, 3, 3, 2, 0, 0, True, False, 0, 384),   # 3x3 s2 valid into a concat slice
+    (2, 17, 17, 160, 160, 1, 7, 1, 0, 3, True, False, 0, 0),
+    (2, 17, 17, 160, 192, 7, 1, 1, 3, 0, True, False, 0, 576),
+    (3, 8, 8, 448, 384, 3, 3, 1, 1, 1, True, False, 0, 0),
+    (2, 8, 8, 384, 384, 1, 3, 1, 0, 1, True, False, 0, 1664),
+    (2, 8, 8, 384, 384, 3, 1, 1, 1, 0, True, False, 0, 1664),
+    (2, 73, 73, 80, 192, 3, 3, 1, 0, 0, True, False, 0, 0),
+    (1, 147, 147, 32, 64, 3, 3, 1, 1, 1, True, False, 0, 0),
+    (2, 17, 17, 192, 320, 3, 3, 2, 0, 0, True, False, 576, 0),   # input is a channel slice of a wider buffer
+    (1, 5, 5, 64, 32, 1, 1, 1, 0, 0, False, False, 0, 0),        # tiny: one partial M tile
+]
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES, ids=lambda s: "x".join(map(str, s[:10])))
+def test_conv_cuda_core_vs_torch(shape):
+    rng = np.random.default_rng(hash(shape) % 2**32)
+    case = _conv_case(rng, *shape)
+    out = _run_conv(0, case)
+    cout = shape[4]
+    got = out[..., :cout].float()
+    tol = 2e-2 * max(1.0, case["ref"].abs().max().item())  # one bf16 rounding of the output
+    assert (got - case["ref"]).abs().max().item() <= tol
+    if shape[13]:
+        assert (out[..., cout:].float() == 7.0).all()  # neighbours of the channel slice untouched
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES, ids=lambda s: "x".join(map(str, s[:10])))
+def test_conv_tcgen05_vs_cuda_core_and_torch(shape):
+    rng = np.random.default_rng(hash(shape) % 2**32)
+    case = _conv_case(rng, *shape)
+    base = _run_conv(0, case)
+    out = _run_conv(1, case)
+    cout = shape[4]
+    ref = case["ref"]
+    got = out[..., :cout].float()
+    tol = 2e-2 * max(1.0, ref.abs().max().item())
+    assert (got - ref).abs().max().item() <= tol
+    # same bf16 operands, fp32 accumulation in both kernels: equal up to summation order
+    d = (got - base[..., :cout].float()).abs().max().item()
+    assert d <= 1.6e-2 * max(1.0, ref.abs().max().item()), d
+    if shape[13]:
+        assert (out[..., cout:].float() == 7.0).all()

@@ -1,0 +1,123 @@
+"""End-to-end parity on the 200 bundled images, through the C ABI, against the
+committed oracle vectors (tests/golden/*_oracle.npz):
+
+  fp32 check mode : logits within 1e-3 relative (max|d| / max|ref|)
+  bf16 modes      : softmax within 2e-2 max-abs (BASELINE.json tolerance); logits
+                    reported relative; identical top-1 on all 200 images
+and per-layer taps against the oracle run live on a few images."""
+import numpy as np
+import pytest
+
+from conftest import pkg
+from oracle import keras_nets, frontend as ofe
+
+pytestmark = pytest.mark.gpu
+
+MODES = {
+    "fp32_check": dict(fp32_check=True),
+    "bf16_cuda_core": dict(tensor_cores=False),
+    "bf16_tcgen05": dict(),
+}
+
+
+def softmax(l):
+    e = np.exp(l - l.max(1, keepdims=True))
+    return e / e.sum(1, keepdims=True)
+
+
+@pytest.mark.parametrize("mode", list(MODES))
+@pytest.mark.parametrize("model", ["ResNet50", "InceptionV3"])
+def test_all_200_images(model, mode, images, oracle_golden):
+    g = oracle_golden[model]
+    kw = pkg("keras_weights")
+    W = kw.generate(model, str(g["preset"]), int(g["seed"]))
+    eng = pkg("engine").Engine(model, max_batch=200, micro_batch=32, weights=W, **MODES[mode])
+    try:
+        idx, prob, probs = eng.predict_images(images, want_probs=True)
+        logits = eng.logits(len(images)).cpu().numpy()
+    finally:
+        eng.close()
+    ref_logits = g["logits"]
+    ref_probs = softmax(ref_logits)
+    rel = np.abs(logits - ref_logits).max() / np.abs(ref_logits).max()
+    dsm = np.abs(probs - ref_probs).max()
+    top1_same = int((idx[:, 0] == g["top5_idx"][:, 0]).sum())
+    top5_same = int(sum(set(a) == set(b) for a, b in zip(idx, g["top5_idx"])))
+    print(f"\n{model} {mode}: logits rel {rel:.3e}  softmax max-abs {dsm:.3e}  top1 {top1_same}/200  top5-set {top5_same}/200")
+    assert np.isfinite(logits).all()
+    if mode == "fp32_check":
+        assert rel <= 1e-3
+        assert dsm <= 1e-3
+    else:
+        assert dsm <= 2e-2
+        assert rel <= 3e-2
+    assert top1_same == 200
+    # the engine's top-5 is consistent with its own softmax, ties -> larger index
+    for r in range(0, 200, 17):
+        order = np.argsort(probs[r], kind="stable")[-5:][::-1]
+        assert list(order) == list(idx[r])
+        assert np.array_equal(prob[r], probs[r][order])
+
+
+@pytest.mark.parametrize("mode", ["fp32_check", "bf16_tcgen05"])
+@pytest.mark.parametrize("model", ["ResNet50", "InceptionV3"])
+def test_layer_taps(model, mode, images):
+    """Intermediate tensors against the oracle, relative to each tensor's own scale."""
+    kw = pkg("keras_weights")
+    W = kw.generate(model)
+    sel = [images[3], images[150], images[77]]
+    size, pmode = ofe.MODEL_INPUT[model]
+    x = np.stack([ofe.preprocess(ofe.resize_nearest_tables(im, size), pmode) for im in sel])
+    taps = {}
+    keras_nets.forward(model, W, x, taps)
+    eng = pkg("engine").Engine(model, max_batch=4, micro_batch=4, weights=W, keep_all=True, **MODES[mode])
+    try:
+        eng.predict_images(sel)
+        have = eng.tensors()
+        checked = 0
+        worst = 0.0
+        for name, ref in taps.items():
+            if name not in have or ref.ndim != 4:
+                continue
+            got = eng.read_tensor(name, len(sel))
+            assert got.shape == ref.shape, name
+            rel = np.abs(got - ref).max() / max(np.abs(ref).max(), 1e-20)
+            worst = max(worst, rel)
+            assert rel <= (1e-3 if mode == "fp32_check" else 4e-2), (name, rel)
+            checked += 1
+        print(f"\n{model} {mode}: {checked} taps, worst rel {worst:.3e}")
+        assert checked >= 10
+    finally:
+        eng.close()
+
+
+def test_results_do_not_depend_on_micro_batch(images):
+    kw = pkg("keras_weights")
+    W = kw.generate("InceptionV3")
+    outs = []
+    for mb in (1, 5, 16):
+        eng = pkg("engine").Engine("InceptionV3", max_batch=16, micro_batch=mb, weights=W)
+        try:
+            outs.append(eng.predict_images(images[100:113], want_probs=True)[2])
+        finally:
+            eng.close()
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+
+
+def test_folding_stress_fp32(images):
+    """Non-trivial biases and BN statistics: folding checked in fp32 mode."""
+    from oracle import models_ref
+    kw = pkg("keras_weights")
+    for model in ("ResNet50", "InceptionV3"):
+        W = kw.generate(model, "folding_stress", 3)
+        sel = images[:6]
+        _, ref_logits = models_ref.predict_arrays(model, sel, W, batch=6)
+        eng = pkg("engine").Engine(model, max_batch=8, weights=W, fp32_check=True)
+        try:
+            eng.predict_images(sel)
+            logits = eng.logits(len(sel)).cpu().numpy()
+        finally:
+            eng.close()
+        rel = np.abs(logits - ref_logits).max() / np.abs(ref_logits).max()
+        print(f"\n{model} folding_stress fp32: logits rel {rel:.3e}")
+        assert rel <= 1e-3
