@@ -75,6 +75,10 @@ _SIGS = {
     "dml_input_tensor": [_vp, C.POINTER(_vp), C.POINTER(_i)],
     "dml_logits": [_vp, C.POINTER(_vp)],
     "dml_launch_count": [_vp, C.POINTER(_i64)],
+    "dml_num_ops": [_vp, C.POINTER(_i)],
+    "dml_op_info": [_vp, _i, C.c_char_p, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i64), C.POINTER(_i64),
+                    C.POINTER(_i64)],
+    "dml_profile_forward": [_vp, _i, _vp, _vp, _vp, _i, _vp],
     "dml_conv2d_bf16": [_i, _vp, _vp, _vp, _vp, _vp] + [_i] * 17 + [_vp],
     "dml_sync": [_vp],
 }

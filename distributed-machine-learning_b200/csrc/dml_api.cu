@@ -82,6 +82,21 @@ struct dml_engine {
   size_t off_lut = 0, off_input = 0, off_arena = 0, off_pooled = 0, off_logits = 0, off_tc = 0, ws_need = 0;
   int64_t launches = 0;
   dml::TcPlan tc;  // tensor maps etc. for the tcgen05 path
+  // profiling (dml_profile_forward): one event pair per op launch
+  bool profiling = false;
+  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof;
+
+  void prof_begin(int op, cudaStream_t s) {
+    if (!profiling) return;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    cudaEventRecord(a, s);
+    prof.push_back({op, {a, b}});
+  }
+  void prof_end(cudaStream_t s) {
+    if (profiling) cudaEventRecord(prof.back().second.second, s);
+  }
 
   void* tensor_ptr(int t, int img0) const {
     const dml::Tensor& tt = net.tensors[t];
@@ -109,6 +124,7 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
     const dml::Op& op = net.ops[oi];
     const dml::Tensor& ti = net.tensors[op.in];
     const dml::Tensor& to = net.tensors[op.out];
+    e->prof_begin((int)oi, s);
     if (op.kind == dml::OP_CONV) {
       dml::ConvParams p{};
       p.in = e->tensor_ptr(op.in, img0);
@@ -145,6 +161,7 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
                       ti.h * ti.w, ti.c, ti.c_pitch, e->fp32, s);
       e->launches += 1;
     }
+    e->prof_end(s);
   }
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -155,9 +172,13 @@ int run_head(dml_engine* e, int n, float* d_probs, int32_t* d_idx, float* d_prob
   const float* pooled = reinterpret_cast<const float*>(e->ws + e->off_pooled);
   float* logits = reinterpret_cast<float*>(e->ws + e->off_logits);
   int cin = net.tensors[net.pooled_tensor].c;
+  e->prof_begin((int)net.ops.size(), s);
   dml::launch_fc(pooled, reinterpret_cast<const float*>(e->wts + net.fc_w_off),
                  reinterpret_cast<const float*>(e->wts + net.fc_b_off), logits, n, cin, s);
+  e->prof_end(s);
+  e->prof_begin((int)net.ops.size() + 1, s);
   dml::launch_softmax_top5(logits, d_probs, d_idx, d_prob, n, s);
+  e->prof_end(s);
   e->launches += 2;
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -168,12 +189,13 @@ int run_pre(dml_engine* e, const uint8_t* d_pixels, const int64_t* d_img_off, co
   dml::PreParams p{};
   const int S = e->net.input_size;
   p.pixels = d_pixels;
-  p.img_off = d_img_off + img0;
-  p.hw = d_hw + 2 * img0;
-  p.xtab = d_xtab + (size_t)img0 * S;
-  p.ytab = d_ytab + (size_t)img0 * S;
-  p.out = e->tensor_ptr(e->net.input_tensor, img0);
-  p.n = cnt; p.S = S; p.caffe = e->net.mode == 0;
+  p.img_off = d_img_off;
+  p.hw = d_hw;
+  p.xtab = d_xtab;
+  p.ytab = d_ytab;
+  p.out = e->tensor_ptr(e->net.input_tensor, 0);
+  p.n = img0 + cnt; p.S = S; p.caffe = e->net.mode == 0;
+  p.img_begin = img0; p.img_end = img0 + cnt;
   dml::launch_preprocess(p, reinterpret_cast<const float*>(e->ws + e->off_lut), e->fp32, s);
   e->launches += 1;
   CUDA_TRY(cudaGetLastError());
@@ -451,6 +473,81 @@ int dml_logits(dml_engine* e, float** dev_ptr) {
   if (!e || !dev_ptr) return fail(DML_EINVAL, "NULL argument");
   if (!e->ws) return fail(DML_ESTATE, "no workspace bound");
   *dev_ptr = reinterpret_cast<float*>(e->ws + e->off_logits);
+  return 0;
+}
+
+int dml_num_ops(dml_engine* e, int* n) {
+  if (!e || !n) return fail(DML_EINVAL, "NULL argument");
+  *n = (int)e->net.ops.size() + 2;
+  return 0;
+}
+
+int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* impl, int64_t* macs_per_img,
+                int64_t* act_bytes_per_img, int64_t* weight_bytes) {
+  if (!e) return fail(DML_EINVAL, "engine is NULL");
+  const dml::Net& net = e->net;
+  const int nops = (int)net.ops.size();
+  if (i < 0 || i >= nops + 2) return fail(DML_EINVAL, "op index %d out of range", i);
+  std::string nm;
+  int k = 0, im = 0;
+  int64_t macs = 0, ab = 0, wb = 0;
+  const int cin_fc = net.tensors[net.pooled_tensor].c;
+  if (i == nops) {
+    nm = "predictions"; k = 4; macs = (int64_t)cin_fc * 1000; ab = (int64_t)cin_fc * 4 + 4000; wb = (int64_t)cin_fc * 4000 + 4000;
+  } else if (i == nops + 1) {
+    nm = "softmax_top5"; k = 5; ab = 4000 + 40;
+  } else {
+    const dml::Op& op = net.ops[i];
+    const dml::Tensor& ti = net.tensors[op.in];
+    const dml::Tensor& to = net.tensors[op.out];
+    nm = op.name; k = (int)op.kind;
+    int64_t in_b = (int64_t)ti.h * ti.w * ti.c * e->act_bytes;
+    int64_t out_b = op.kind == dml::OP_GAP ? (int64_t)to.c * 4 : (int64_t)to.h * to.w * to.c * e->act_bytes;
+    ab = in_b + out_b + (op.res >= 0 ? out_b : 0);
+    if (op.kind == dml::OP_CONV) {
+      macs = (int64_t)to.h * to.w * op.cout * op.kh * op.kw * op.cin;
+      wb = (int64_t)op.cout * op.kh * op.kw * op.cin * (e->fp32 ? 4 : 2) + op.cout * 4;
+      im = (e->use_tc && dml::tc_supported(op)) ? 1 : 0;
+    }
+  }
+  if (name && name_cap > 0) snprintf(name, name_cap, "%s", nm.c_str());
+  if (kind) *kind = k;
+  if (impl) *impl = im;
+  if (macs_per_img) *macs_per_img = macs;
+  if (act_bytes_per_img) *act_bytes_per_img = ab;
+  if (weight_bytes) *weight_bytes = wb;
+  return 0;
+}
+
+int dml_profile_forward(dml_engine* e, int n, int32_t* d_top5_idx, float* d_top5_prob, float* op_ms, int cap,
+                        void* stream) {
+  if (int rc = check_ready(e, n)) return rc;
+  if (!d_top5_idx || !d_top5_prob) return fail(DML_EINVAL, "NULL output pointer");
+  const int nops = (int)e->net.ops.size() + 2;
+  if (!op_ms || cap < nops) return fail(DML_EINVAL, "op_ms must hold at least %d floats", nops);
+  CUDA_TRY(cudaSetDevice(e->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  for (int i = 0; i < nops; ++i) op_ms[i] = 0.f;
+  e->profiling = true;
+  e->prof.clear();
+  int rc = 0;
+  for (int i0 = 0; i0 < n && rc == 0; i0 += e->micro_batch) {
+    int cnt = n - i0 < e->micro_batch ? n - i0 : e->micro_batch;
+    rc = run_layers(e, i0, cnt, s);
+  }
+  if (rc == 0) rc = run_head(e, n, nullptr, d_top5_idx, d_top5_prob, s);
+  e->profiling = false;
+  cudaError_t ce = cudaStreamSynchronize(s);
+  for (auto& pr : e->prof) {
+    float ms = 0.f;
+    if (ce == cudaSuccess && rc == 0 && cudaEventElapsedTime(&ms, pr.second.first, pr.second.second) == cudaSuccess)
+      op_ms[pr.first] += ms;
+    cudaEventDestroy(pr.second.first);
+    cudaEventDestroy(pr.second.second);
+  }
+  e->prof.clear();
+  if (rc) return rc;
+  CUDA_TRY(ce);
   return 0;
 }
 

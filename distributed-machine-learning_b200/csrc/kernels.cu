@@ -29,9 +29,14 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p, const floa
   __syncthreads();
   const int S = p.S;
   const int64_t per_img = (int64_t)S * S * 3;
-  const int64_t total = per_img * p.n;
-  int64_t e0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
-  if (e0 >= total) return;
+  // Element range of this launch inside the whole tensor; threads own 8-element
+  // groups aligned in the GLOBAL element index so that full groups are 16-byte stores
+  // even when an image starts at an odd element (299*299*3 is odd).
+  const int64_t lo = per_img * p.img_begin, hi = per_img * p.img_end;
+  const int64_t g0 = (lo / 8) * 8 + ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (g0 >= hi) return;
+  const int64_t e0 = g0 < lo ? lo : g0;
+  const int64_t e1 = g0 + 8 < hi ? g0 + 8 : hi;
   int img = (int)(e0 / per_img);
   int rem = (int)(e0 - (int64_t)img * per_img);
   int pix = rem / 3;
@@ -44,14 +49,14 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p, const floa
   int sy = p.ytab[img * S + y];
   int sx = p.xtab[img * S + x];
   TO vals[8];
-  int cnt = 0;
+  const int first = (int)(e0 - g0), cnt = (int)(e1 - e0);
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    if (e0 + i < total) {
+    vals[i] = from_f<TO>(0.f);
+    if (i >= first && i < first + cnt) {
       int sc = caffe ? 2 - ch : ch;
       uint8_t v = src[((int64_t)sy * W + sx) * 3 + sc];
       vals[i] = from_f<TO>(lut[ch * 256 + v]);
-      cnt = i + 1;
       if (++ch == 3) {
         ch = 0;
         if (++x == S) {
@@ -59,20 +64,18 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p, const floa
           if (++y == S) {
             y = 0;
             ++img;
-            if (img < p.n) {
+            if (img < p.img_end) {
               src = p.pixels + p.img_off[img];
               W = p.hw[2 * img + 1];
             }
           }
-          if (img < p.n) sy = p.ytab[img * S + y];
+          if (img < p.img_end) sy = p.ytab[img * S + y];
         }
-        if (img < p.n) sx = p.xtab[img * S + x];
+        if (img < p.img_end) sx = p.xtab[img * S + x];
       }
-    } else {
-      vals[i] = from_f<TO>(0.f);
     }
   }
-  TO* out = reinterpret_cast<TO*>(p.out) + e0;
+  TO* out = reinterpret_cast<TO*>(p.out) + g0;
   if (cnt == 8) {
     if (sizeof(TO) == 2) {
       *reinterpret_cast<uint4*>(out) = *reinterpret_cast<uint4*>(vals);
@@ -81,7 +84,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p, const floa
       reinterpret_cast<uint4*>(out)[1] = reinterpret_cast<uint4*>(vals)[1];
     }
   } else {
-    for (int i = 0; i < cnt; ++i) out[i] = vals[i];
+    for (int i = first; i < first + cnt; ++i) out[i] = vals[i];
   }
 }
 
@@ -348,8 +351,10 @@ __global__ void __launch_bounds__(256) softmax_top5_kernel(const float* __restri
 }  // namespace
 
 void launch_preprocess(const PreParams& p, const float* d_lut, bool fp32_out, cudaStream_t s) {
-  int64_t total = (int64_t)p.n * p.S * p.S * 3;
-  int64_t threads = (total + 7) / 8;
+  int64_t per_img = (int64_t)p.S * p.S * 3;
+  int64_t lo = per_img * p.img_begin, hi = per_img * p.img_end;
+  int64_t threads = (hi - (lo / 8) * 8 + 7) / 8;
+  if (threads <= 0) return;
   unsigned blocks = (unsigned)((threads + 255) / 256);
   if (fp32_out) preprocess_kernel<float><<<blocks, 256, 0, s>>>(p, d_lut, p.caffe);
   else preprocess_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(p, d_lut, p.caffe);

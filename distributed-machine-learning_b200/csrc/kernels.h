@@ -31,8 +31,9 @@ struct PreParams {
   const int32_t* hw;    // (H, W) per image
   const int32_t* xtab;  // n x S
   const int32_t* ytab;  // n x S
-  void* out;            // n x S x S x 3
-  int n, S;
+  void* out;            // base of the whole input tensor (image 0), 16-byte aligned
+  int n, S;             // n = images in the tensor the tables cover
+  int img_begin, img_end;  // images [img_begin, img_end) are produced by this launch
   int caffe;            // 1: output channel c reads source channel 2-c (RGB->BGR)
 };
 

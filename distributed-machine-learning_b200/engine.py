@@ -115,6 +115,33 @@ class Engine:
                                     self.d_probs.data_ptr() if want_probs else None, self.d_idx.data_ptr(),
                                     self.d_prob.data_ptr(), self.stream.cuda_stream))
 
+    def infer_ptrs(self, pixels, img_off, hw, xtab, ytab, n: int, want_probs: bool = False):
+        """dml_infer over caller-owned device tensors (uint8 pixels, int64 offsets, int32 sizes/tables)."""
+        _lib.check(self.l.dml_infer(self.h, pixels.data_ptr(), img_off.data_ptr(), hw.data_ptr(), xtab.data_ptr(),
+                                    ytab.data_ptr(), n, self.d_probs.data_ptr() if want_probs else None,
+                                    self.d_idx.data_ptr(), self.d_prob.data_ptr(), self.stream.cuda_stream))
+
+    def pin(self, hb: frontend.HostBatch) -> frontend.HostBatch:
+        """Moves a HostBatch's arrays into pinned host memory (async H2D copies need it)."""
+        torch = _torch()
+        for name in ("pixels", "img_off", "hw", "xtab", "ytab"):
+            t = torch.from_numpy(getattr(hb, name)).pin_memory()
+            setattr(hb, name, t.numpy())
+            setattr(hb, "_pin_" + name, t)
+        return hb
+
+    def predict_host_batch(self, hb: frontend.HostBatch):
+        """One step end to end: H2D of the batch, dml_infer, D2H of the top-5, sync.
+        Returns views of the pinned result buffers (valid until the next call)."""
+        torch = _torch()
+        self.upload(hb)
+        self.infer_device(hb.n)
+        with torch.cuda.stream(self.stream):
+            self.h_idx[:hb.n].copy_(self.d_idx[:hb.n], non_blocking=True)
+            self.h_prob[:hb.n].copy_(self.d_prob[:hb.n], non_blocking=True)
+        self.stream.synchronize()
+        return self.h_idx[:hb.n].numpy(), self.h_prob[:hb.n].numpy()
+
     def predict_images(self, images, want_probs: bool = False):
         """uint8 HxWx3 arrays -> (top5_idx [n,5] int32, top5_prob [n,5] fp32[, probs [n,1000]])."""
         torch = _torch()
@@ -182,6 +209,28 @@ class Engine:
         full = torch.zeros(n * h * w * cp, dtype=dt, device=flat.device)
         full[:flat.numel()] = flat
         return full.view(n, h, w, cp)[..., :c].float().cpu().numpy()
+
+    def ops(self):
+        """[(name, kind, impl, macs_per_img, act_bytes_per_img, weight_bytes)] of the layer plan."""
+        n = C.c_int()
+        _lib.check(self.l.dml_num_ops(self.h, C.byref(n)))
+        buf = C.create_string_buffer(128)
+        out = []
+        for i in range(n.value):
+            k, im = C.c_int(), C.c_int()
+            macs, ab, wb = C.c_int64(), C.c_int64(), C.c_int64()
+            _lib.check(self.l.dml_op_info(self.h, i, buf, 128, C.byref(k), C.byref(im), C.byref(macs), C.byref(ab),
+                                          C.byref(wb)))
+            out.append((buf.value.decode(), k.value, im.value, macs.value, ab.value, wb.value))
+        return out
+
+    def profile_forward(self, n: int):
+        """Per-op milliseconds of one forward over the current input tensor (CUDA events around each launch)."""
+        nops = len(self.ops())
+        ms = np.zeros(nops, dtype=np.float32)
+        _lib.check(self.l.dml_profile_forward(self.h, n, self.d_idx.data_ptr(), self.d_prob.data_ptr(), ms.ctypes.data,
+                                              nops, self.stream.cuda_stream))
+        return ms
 
     def launch_count(self) -> int:
         v = C.c_int64()

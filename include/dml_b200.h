@@ -130,6 +130,20 @@ int dml_input_tensor(dml_engine* e, void** dev_ptr, int* elem_bytes);
 /* Logits (pre-softmax), n x 1000 fp32, valid after dml_forward / dml_infer. */
 int dml_logits(dml_engine* e, float** dev_ptr);
 
+/* Number of ops in the layer plan and, for op i: name, kind (0 conv, 1 max-pool,
+ * 2 avg-pool, 3 global-avg-pool, 4 dense, 5 softmax+top5), which kernel runs it
+ * (0 CUDA-core, 1 tcgen05), algorithmic MACs per image and algorithmic bytes
+ * per image (activations in + out, residual) plus weight bytes per launch. */
+int dml_num_ops(dml_engine* e, int* n);
+int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* impl, int64_t* macs_per_img,
+                int64_t* act_bytes_per_img, int64_t* weight_bytes);
+
+/* dml_forward with a CUDA-event pair around every launch: op_ms[i] receives the
+ * milliseconds op i took, summed over the micro-batches (cap >= dml_num_ops).
+ * Synchronous; for bench.py's roofline, not for production. */
+int dml_profile_forward(dml_engine* e, int n, int32_t* d_top5_idx, float* d_top5_prob, float* op_ms, int cap,
+                        void* stream);
+
 /* Kernels launched by this engine since creation (all of them ours). */
 int dml_launch_count(dml_engine* e, int64_t* launches);
 
