@@ -258,6 +258,218 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
   }
 }
 
+
+// ------------------- v2: persistent, warp-specialised kernel -------------------
+// One CTA per SM walks tiles tile = blockIdx.x + i*gridDim.x (N tiles of one M tile
+// adjacent, so concurrent CTAs share the A rows in L2).  The smem ring and the
+// TMA producer run ahead across tile boundaries; two TMEM accumulators let the
+// MMA warp start tile i+1 while the epilogue warps drain tile i.  The epilogue
+// stages bf16 rows in swizzled shared memory and writes them with TMA stores
+// (full 128-byte lines; rows past the tensor end are clipped by the TMA unit).
+struct TcV2Params {
+  const float* bias;
+  const __nv_bfloat16* res;
+  int M, ho, wo;
+  int stride, pad_h, pad_w;
+  int kw, num_kb, cpb;
+  int bn, res_pitch, relu;
+  int stages, tmem_cols, acc_stride;
+  int m_tiles, n_tiles;
+  int cw;  // epilogue chunk width in columns: 64 / 32 / 16 (TMA store swizzle 128B / 64B / 32B)
+};
+
+constexpr int OUT_BUF_BYTES = 4096;  // 32 rows x 128 B
+constexpr int OUT_STAGING_BYTES = 4 * 2 * OUT_BUF_BYTES;
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int x, int y) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(src), "r"(x),
+               "r"(y)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_constant__ CUtensorMap map_a,
+                                                                 const __grid_constant__ CUtensorMap map_b,
+                                                                 const __grid_constant__ CUtensorMap map_o,
+                                                                 const TcV2Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int stages = p.stages;
+  const uint32_t b_stage_bytes = (uint32_t)p.bn * 128u;
+  const uint32_t sA = base;
+  const uint32_t sB = sA + (uint32_t)stages * A_STAGE_BYTES;
+  const uint32_t sO = sB + (uint32_t)stages * b_stage_bytes;
+  const uint32_t bars = sO + OUT_STAGING_BYTES;
+  const uint32_t full0 = bars, empty0 = bars + 8u * stages;
+  const uint32_t tfull0 = bars + 16u * stages, tempty0 = tfull0 + 16u;
+  const uint32_t tmem_slot = tempty0 + 16u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = p.m_tiles * p.n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_o) : "memory");
+    for (int i = 0; i < stages; ++i) {
+      mbar_init(full0 + 8u * i, 1);
+      mbar_init(empty0 + 8u * i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(tfull0 + 8u * i, 1);
+      mbar_init(tempty0 + 8u * i, 4);  // one arrive per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(p.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---------------- TMA producer ----------------
+      const int howo = p.ho * p.wo;
+      const uint32_t tx_bytes = A_STAGE_BYTES + b_stage_bytes;
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
+        const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
+        const int img = m0 / howo;
+        const int rem = m0 - img * howo;
+        const int oh = rem / p.wo, ow = rem - oh * p.wo;
+        const int w_base = ow * p.stride - p.pad_w, h_base = oh * p.stride - p.pad_h;
+        int tap = 0, cb = 0, r = 0, sx = 0;
+        for (int j = 0; j < p.num_kb; ++j, ++it) {
+          const uint32_t s = it % (uint32_t)stages;
+          const uint32_t ph = (it / (uint32_t)stages) & 1u;
+          mbar_wait(empty0 + 8u * s, ph ^ 1u);
+          mbar_arrive_expect_tx(full0 + 8u * s, tx_bytes);
+          tma_load_im2col_4d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base, img,
+                             (uint16_t)sx, (uint16_t)r);
+          tma_load_2d(sB + s * b_stage_bytes, &map_b, full0 + 8u * s, j * BLOCK_K, n0);
+          if (++cb == p.cpb) {
+            cb = 0;
+            ++tap;
+            if (++sx == p.kw) { sx = 0; ++r; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ---------------- MMA issuer ----------------
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+      uint32_t it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+        const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+        mbar_wait(tempty0 + 8u * a, aph ^ 1u);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
+        for (int j = 0; j < p.num_kb; ++j, ++it) {
+          const uint32_t s = it % (uint32_t)stages;
+          const uint32_t ph = (it / (uint32_t)stages) & 1u;
+          mbar_wait(full0 + 8u * s, ph);
+          tc_fence_after();
+          const uint64_t da = make_sw128_desc(sA + s * A_STAGE_BYTES);
+          const uint64_t db = make_sw128_desc(sB + s * b_stage_bytes);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k)
+            umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((j | k) != 0));
+          umma_commit(empty0 + 8u * s);
+        }
+        umma_commit(tfull0 + 8u * a);
+      }
+    }
+  } else {
+    // ---------------- epilogue warps ----------------
+    const int q = warp & 3;
+    const uint32_t my_out = sO + (uint32_t)q * 2u * OUT_BUF_BYTES;
+    const int cw = p.cw;
+    const uint32_t row_bytes = (uint32_t)cw * 2u;
+    const uint32_t swz = cw == 64 ? (uint32_t)(lane & 7) : (cw == 32 ? (uint32_t)((lane >> 1) & 3) : (uint32_t)((lane >> 2) & 1));
+    uint32_t lt = 0, nstore = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
+      const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
+      const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+      const long long m = (long long)m0 + q * 32 + lane;
+      const bool row_ok = m < p.M;
+      const __nv_bfloat16* rrow = (p.res && row_ok) ? p.res + m * p.res_pitch + n0 : nullptr;
+      mbar_wait(tfull0 + 8u * a, aph);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
+      for (int c0 = 0; c0 < p.bn; c0 += cw, ++nstore) {
+        const uint32_t sbuf = my_out + (nstore & 1u) * OUT_BUF_BYTES;
+        // the TMA store that last read this buffer (two stores ago) must be done reading
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        __syncwarp();
+        for (int g = 0; g < cw; g += 16) {
+          uint32_t v[16];
+          tmem_ld16(t_row + (uint32_t)(c0 + g), v);
+          float f[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]) + __ldg(p.bias + n0 + c0 + g + i);
+          if (rrow) {
+            uint4 r0 = *reinterpret_cast<const uint4*>(rrow + c0 + g);
+            uint4 r1 = *reinterpret_cast<const uint4*>(rrow + c0 + g + 8);
+            const __nv_bfloat16* rb0 = reinterpret_cast<const __nv_bfloat16*>(&r0);
+            const __nv_bfloat16* rb1 = reinterpret_cast<const __nv_bfloat16*>(&r1);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              f[i] += __bfloat162float(rb0[i]);
+              f[8 + i] += __bfloat162float(rb1[i]);
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
+          }
+          uint32_t pk[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+            pk[i] = *reinterpret_cast<uint32_t*>(&h2);
+          }
+          const uint32_t j0 = (uint32_t)(g >> 3);  // 16-byte chunk index of this group inside the row
+          const uint32_t rowaddr = sbuf + (uint32_t)lane * row_bytes;
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + ((j0 ^ swz) << 4)), "r"(pk[0]), "r"(pk[1]),
+                       "r"(pk[2]), "r"(pk[3])
+                       : "memory");
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((j0 + 1u) ^ swz) << 4)), "r"(pk[4]),
+                       "r"(pk[5]), "r"(pk[6]), "r"(pk[7])
+                       : "memory");
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&map_o, sbuf, n0 + c0, m0 + q * 32);
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+      }
+      // every tcgen05.ld of this warp has completed (wait::ld): hand the accumulator back
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty0 + 8u * a);
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+  }
+}
+
 }  // namespace
 
 // ------------------------------- host side ---------------------------------
@@ -267,12 +479,30 @@ PFN_cuTensorMapEncodeTiled g_encode_tiled = nullptr;
 PFN_cuTensorMapEncodeIm2col g_encode_im2col = nullptr;
 int g_driver_version = 0;
 
+int g_num_sms = 148;
+
 int pick_bn(int cout, int override_bn) {
   if (override_bn > 0) return (cout % override_bn == 0 && override_bn % 16 == 0 && override_bn <= 256) ? override_bn : 0;
   if (cout <= 128) return cout;
   for (int bn = 128; bn >= 16; bn -= 16)
     if (cout % bn == 0) return bn;
   return 0;
+}
+
+// Persistent kernel: the widest N tile that still gives every SM a tile.
+int pick_bn_v2(int cout, long long m_tiles, int override_bn) {
+  if (override_bn > 0) return pick_bn(cout, override_bn);
+  int best = 0;
+  long long best_tiles = -1;
+  for (int bn = cout < 256 ? cout : 256; bn >= 16; bn -= 16) {
+    if (cout % bn) continue;
+    long long tiles = m_tiles * (cout / bn);
+    if (tiles >= g_num_sms) return bn;
+    if (bn >= 64 || best == 0) {
+      if (tiles > best_tiles) { best_tiles = tiles; best = bn; }
+    }
+  }
+  return best;
 }
 
 }  // namespace
@@ -301,6 +531,11 @@ int tc_init() {
   }
   cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(conv_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc2_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0)
+    g_num_sms = sms;
   return 0;
 }
 
@@ -309,20 +544,49 @@ size_t tc_scratch_bytes(const Net&, int) { return 0; }
 int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune& tune) {
   if (!g_encode_tiled) return tc_fail("tc_init was not called");
   TcOpPlan op;
-  op.bn = pick_bn(p.cout, tune.bn);
+  op.version = tune.version == 1 ? 1 : 2;
+  const long long M_cap = (long long)n_capacity * p.ho * p.wo;
+  const long long m_tiles_cap = (M_cap + BLOCK_M - 1) / BLOCK_M;
+  op.bn = op.version == 1 ? pick_bn(p.cout, tune.bn) : pick_bn_v2(p.cout, m_tiles_cap, tune.bn);
   if (op.bn == 0) return tc_fail("no N tile for cout = %d (override %d)", p.cout, tune.bn);
   if (p.cin_pad % BLOCK_K) return tc_fail("cin_pad = %d is not a multiple of %d", p.cin_pad, BLOCK_K);
   op.cpb = p.cin_pad / BLOCK_K;
   const int num_kb = p.kh * p.kw * op.cpb;
   const int stage_bytes = A_STAGE_BYTES + op.bn * 128;
-  int target = op.bn <= 64 ? 3 : (op.bn <= 128 ? 3 : 4);
-  if (tune.stages > 0) target = tune.stages;
-  if (target > num_kb) target = num_kb;
-  while (target > 1 && target * stage_bytes + 2048 > SMEM_LIMIT) --target;
-  op.stages = target;
-  op.smem = (size_t)op.stages * stage_bytes + 1024 /*alignment slack*/ + 16 * op.stages + 64;
-  op.tmem_cols = 32;
-  while (op.tmem_cols < op.bn) op.tmem_cols *= 2;
+  if (op.version == 1) {
+    int target = op.bn <= 64 ? 3 : (op.bn <= 128 ? 3 : 4);
+    if (tune.stages > 0) target = tune.stages;
+    if (target > num_kb) target = num_kb;
+    while (target > 1 && target * stage_bytes + 2048 > SMEM_LIMIT) --target;
+    op.stages = target;
+    op.smem = (size_t)op.stages * stage_bytes + 1024 /*alignment slack*/ + 16 * op.stages + 64;
+    op.tmem_cols = 32;
+    while (op.tmem_cols < op.bn) op.tmem_cols *= 2;
+  } else {
+    const int fixed = 1024 /*alignment slack*/ + OUT_STAGING_BYTES + 256 /*barriers*/;
+    int target = (SMEM_LIMIT - fixed) / stage_bytes;
+    if (target > 8) target = 8;
+    if (tune.stages > 0 && tune.stages < target) target = tune.stages;
+    if (target < 2) return tc_fail("not enough shared memory for 2 stages at bn = %d", op.bn);
+    op.stages = target;
+    op.smem = (size_t)op.stages * stage_bytes + fixed;
+    op.acc_stride = 32;
+    while (op.acc_stride < op.bn) op.acc_stride *= 2;
+    op.tmem_cols = 2 * op.acc_stride;
+    op.cw = op.bn % 64 == 0 ? 64 : (op.bn % 32 == 0 ? 32 : 16);
+    op.m_capacity = (int)M_cap;
+    if (!p.out) return tc_fail("output pointer needed to plan the persistent kernel");
+    cuuint64_t odim[2] = {(cuuint64_t)p.cout, (cuuint64_t)M_cap};
+    cuuint64_t ostr[1] = {(cuuint64_t)p.out_pitch * 2};
+    cuuint32_t obox[2] = {(cuuint32_t)op.cw, 32};
+    cuuint32_t oes[2] = {1, 1};
+    CUtensorMapSwizzle osw = op.cw == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (op.cw == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+    CUresult ro = g_encode_tiled(&op.map_o, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p.out, odim, ostr, obox, oes,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, osw, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (ro != CUDA_SUCCESS)
+      return tc_fail("cuTensorMapEncodeTiled(output) failed (%d): cout=%d M=%lld pitch=%d cw=%d", (int)ro, p.cout, M_cap, p.out_pitch, op.cw);
+  }
 
   // A: NHWC view as (C, W, H, N), im2col mode.  Corner convention as in CUTLASS'
   // make_im2col_tma_copy_desc: lower = -pad, upper = pad - (filter - 1); index 0 = W.
@@ -360,6 +624,27 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
 
 int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s) {
   if (!op.valid) return tc_fail("conv plan is not valid");
+  if (op.version == 2) {
+    TcV2Params k{};
+    k.bias = p.bias;
+    k.res = reinterpret_cast<const __nv_bfloat16*>(p.res);
+    k.M = p.n * p.ho * p.wo;
+    if (k.M > op.m_capacity) return tc_fail("batch of %d images exceeds the planned capacity", p.n);
+    k.ho = p.ho; k.wo = p.wo;
+    k.stride = p.stride; k.pad_h = p.pad_h; k.pad_w = p.pad_w;
+    k.kw = p.kw; k.cpb = op.cpb; k.num_kb = p.kh * p.kw * op.cpb;
+    k.bn = op.bn; k.res_pitch = p.res_pitch; k.relu = p.relu;
+    k.stages = op.stages; k.tmem_cols = op.tmem_cols; k.acc_stride = op.acc_stride;
+    k.m_tiles = (k.M + BLOCK_M - 1) / BLOCK_M;
+    k.n_tiles = p.cout / op.bn;
+    k.cw = op.cw;
+    const int tiles = k.m_tiles * k.n_tiles;
+    const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+    conv_tc2_kernel<<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, k);
+    cudaError_t e2 = cudaGetLastError();
+    if (e2 != cudaSuccess) return tc_fail("conv_tc2_kernel launch: %s", cudaGetErrorString(e2));
+    return 0;
+  }
   TcKernelParams k{};
   k.bias = p.bias;
   k.res = reinterpret_cast<const __nv_bfloat16*>(p.res);
@@ -391,6 +676,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     ConvParams p{};
     p.in = ws + off_arena + ((size_t)net.bufs[ti.buf].offset * micro_batch + ti.c_off) * 2;
     p.w = wts + op.wpack_off;
+    p.out = ws + off_arena + ((size_t)net.bufs[to.buf].offset * micro_batch + to.c_off) * 2;
     p.n = micro_batch; p.hi = ti.h; p.wi = ti.w; p.cin = op.cin; p.in_pitch = ti.c_pitch;
     p.ho = to.h; p.wo = to.w; p.cout = op.cout; p.out_pitch = to.c_pitch;
     p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;

@@ -20,6 +20,12 @@ struct TcOpPlan {
   int tmem_cols = 0;
   int cpb = 0;       // 64-channel blocks per tap
   size_t smem = 0;
+  // v2 (persistent kernel)
+  int version = 2;
+  alignas(64) CUtensorMap map_o;  // tiled map over the output view [M_capacity][cout], pitch = out_pitch
+  int cw = 0;          // epilogue chunk width (columns per TMA store box)
+  int acc_stride = 0;  // TMEM columns between the two accumulators
+  int m_capacity = 0;  // rows the output map covers
 };
 
 struct TcPlan {
@@ -31,6 +37,7 @@ struct TcPlan {
 struct TcTune {
   int bn = 0;
   int stages = 0;
+  int version = 0;  // 1 = one tile per CTA, 2 = persistent (default)
 };
 
 bool tc_supported(const Op& op);

@@ -142,12 +142,13 @@ def test_conv_cuda_core_vs_torch(shape):
         assert (out[..., cout:].float() == 7.0).all()  # neighbours of the channel slice untouched
 
 
+@pytest.mark.parametrize("impl", [1, 2], ids=["tile_per_cta", "persistent"])
 @pytest.mark.parametrize("shape", CONV_SHAPES, ids=lambda s: "x".join(map(str, s[:10])))
-def test_conv_tcgen05_vs_cuda_core_and_torch(shape):
+def test_conv_tcgen05_vs_cuda_core_and_torch(shape, impl):
     rng = np.random.default_rng(hash(shape) % 2**32)
     case = _conv_case(rng, *shape)
     base = _run_conv(0, case)
-    out = _run_conv(1, case)
+    out = _run_conv(impl, case)
     cout = shape[4]
     ref = case["ref"]
     got = out[..., :cout].float()
@@ -156,5 +157,33 @@ def test_conv_tcgen05_vs_cuda_core_and_torch(shape):
     # same bf16 operands, fp32 accumulation in both kernels: equal up to summation order
     d = (got - base[..., :cout].float()).abs().max().item()
     assert d <= 1.6e-2 * max(1.0, ref.abs().max().item()), d
+    if shape[13]:
+        assert (out[..., cout:].float() == 7.0).all()
+
+
+PERSISTENT_CASES = [
+    # shape, tile_n, stages: many tiles per CTA, both accumulators, ring wrap-around, all store widths
+    ((8, 56, 56, 64, 256, 1, 1, 1, 0, 0, True, True, 0, 0), 0, 0),
+    ((8, 56, 56, 64, 256, 1, 1, 1, 0, 0, True, True, 0, 0), 64, 2),
+    ((8, 56, 56, 64, 256, 1, 1, 1, 0, 0, False, False, 0, 0), 256, 0),
+    ((16, 28, 28, 128, 128, 3, 3, 1, 1, 1, True, False, 0, 0), 128, 3),
+    ((16, 28, 28, 128, 128, 3, 3, 1, 1, 1, True, False, 0, 0), 32, 0),
+    ((9, 35, 35, 64, 96, 3, 3, 1, 1, 1, True, False, 0, 160), 0, 0),    # bn 96 -> 32-column boxes
+    ((9, 35, 35, 48, 64, 5, 5, 1, 2, 2, True, False, 0, 32), 16, 2),     # 16-column boxes
+    ((6, 73, 73, 64, 80, 1, 1, 1, 0, 0, True, False, 0, 0), 0, 0),       # bn 80 -> 16-column boxes
+    ((32, 14, 14, 1024, 256, 1, 1, 1, 0, 0, True, False, 0, 0), 0, 0),
+]
+
+
+@pytest.mark.parametrize("case_id", range(len(PERSISTENT_CASES)))
+def test_conv_tcgen05_persistent_tiles(case_id):
+    shape, tile_n, stages = PERSISTENT_CASES[case_id]
+    rng = np.random.default_rng(1234 + case_id)
+    case = _conv_case(rng, *shape)
+    out = _run_conv(2, case, tile_n, stages)
+    cout = shape[4]
+    ref = case["ref"]
+    got = out[..., :cout].float()
+    assert (got - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
     if shape[13]:
         assert (out[..., cout:].float() == 7.0).all()
