@@ -280,7 +280,7 @@ def run_b200(args):
 
 
 def eng_micro(eng, args):
-    return args.micro_batch if args.micro_batch > 0 else 32
+    return args.micro_batch if args.micro_batch > 0 else eng.max_batch
 
 
 def main():

@@ -127,6 +127,15 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+
 // ------------------------------- the kernel --------------------------------
 __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                              const __grid_constant__ CUtensorMap map_b,
@@ -276,6 +285,9 @@ struct TcV2Params {
   int stages, tmem_cols, acc_stride;
   int m_tiles, n_tiles;
   int cw;  // epilogue chunk width in columns: 64 / 32 / 16 (TMA store swizzle 128B / 64B / 32B)
+  int has_res;      // residual tiles are TMA-loaded into shared memory by the producer warp
+  int out_row0;     // first output row of this launch inside the output/residual maps
+  int in_img0;      // first image of this launch inside the input map
 };
 
 constexpr int OUT_BUF_BYTES = 4096;  // 32 rows x 128 B
@@ -293,6 +305,7 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t sr
 __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                  const __grid_constant__ CUtensorMap map_b,
                                                                  const __grid_constant__ CUtensorMap map_o,
+                                                                 const __grid_constant__ CUtensorMap map_r,
                                                                  const TcV2Params p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -301,10 +314,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
   const uint32_t sA = base;
   const uint32_t sB = sA + (uint32_t)stages * A_STAGE_BYTES;
   const uint32_t sO = sB + (uint32_t)stages * b_stage_bytes;
-  const uint32_t bars = sO + OUT_STAGING_BYTES;
+  const uint32_t res_tile_bytes = p.has_res ? (uint32_t)BLOCK_M * (uint32_t)p.bn * 2u : 0u;
+  const uint32_t sR = sO + OUT_STAGING_BYTES;  // 2 residual tiles: [chunk][128 rows][cw*2 bytes], swizzled like the output
+  const uint32_t bars = sR + 2u * res_tile_bytes;
   const uint32_t full0 = bars, empty0 = bars + 8u * stages;
   const uint32_t tfull0 = bars + 16u * stages, tempty0 = tfull0 + 16u;
-  const uint32_t tmem_slot = tempty0 + 16u;
+  const uint32_t rfull0 = tempty0 + 16u, rempty0 = rfull0 + 16u;
+  const uint32_t tmem_slot = rempty0 + 16u;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.m_tiles * p.n_tiles;
@@ -320,6 +336,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull0 + 8u * i, 1);
       mbar_init(tempty0 + 8u * i, 4);  // one arrive per epilogue warp
+      mbar_init(rfull0 + 8u * i, 1);
+      mbar_init(rempty0 + 8u * i, 4);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -339,10 +357,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
       // ---------------- TMA producer ----------------
       const int howo = p.ho * p.wo;
       const uint32_t tx_bytes = A_STAGE_BYTES + b_stage_bytes;
-      uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      uint32_t it = 0, lt = 0;
+      const uint32_t chunk_bytes = (uint32_t)BLOCK_M * (uint32_t)p.cw * 2u;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
         const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
         const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
+        if (p.has_res) {
+          // whole residual tile of this output tile, one box per column chunk
+          const uint32_t rb = lt & 1u, rph = (lt >> 1) & 1u;
+          mbar_wait(rempty0 + 8u * rb, rph ^ 1u);
+          mbar_arrive_expect_tx(rfull0 + 8u * rb, res_tile_bytes);
+          for (int c = 0, ci = 0; c < p.bn; c += p.cw, ++ci)
+            tma_load_2d(sR + rb * res_tile_bytes + (uint32_t)ci * chunk_bytes, &map_r, rfull0 + 8u * rb, n0 + c,
+                        p.out_row0 + m0);
+        }
         const int img = m0 / howo;
         const int rem = m0 - img * howo;
         const int oh = rem / p.wo, ow = rem - oh * p.wo;
@@ -353,8 +381,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
           const uint32_t ph = (it / (uint32_t)stages) & 1u;
           mbar_wait(empty0 + 8u * s, ph ^ 1u);
           mbar_arrive_expect_tx(full0 + 8u * s, tx_bytes);
-          tma_load_im2col_4d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base, img,
-                             (uint16_t)sx, (uint16_t)r);
+          tma_load_im2col_4d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base,
+                             img + p.in_img0, (uint16_t)sx, (uint16_t)r);
           tma_load_2d(sB + s * b_stage_bytes, &map_b, full0 + 8u * s, j * BLOCK_K, n0);
           if (++cb == p.cpb) {
             cb = 0;
@@ -395,70 +423,94 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
     const uint32_t my_out = sO + (uint32_t)q * 2u * OUT_BUF_BYTES;
     const int cw = p.cw;
     const uint32_t row_bytes = (uint32_t)cw * 2u;
+    const uint32_t chunk_bytes = (uint32_t)BLOCK_M * row_bytes;
     const uint32_t swz = cw == 64 ? (uint32_t)(lane & 7) : (cw == 32 ? (uint32_t)((lane >> 1) & 3) : (uint32_t)((lane >> 2) & 1));
     uint32_t lt = 0, nstore = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
       const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
       const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
-      const long long m = (long long)m0 + q * 32 + lane;
-      const bool row_ok = m < p.M;
-      const __nv_bfloat16* rrow = (p.res && row_ok) ? p.res + m * p.res_pitch + n0 : nullptr;
+      if (p.has_res) mbar_wait(rfull0 + 8u * a, aph);
       mbar_wait(tfull0 + 8u * a, aph);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
-      for (int c0 = 0; c0 < p.bn; c0 += cw, ++nstore) {
+      const uint32_t r_row = sR + a * res_tile_bytes + (uint32_t)(q * 32 + lane) * row_bytes;
+      int ci = 0;
+      for (int c0 = 0; c0 < p.bn; c0 += cw, ++nstore, ++ci) {
         const uint32_t sbuf = my_out + (nstore & 1u) * OUT_BUF_BYTES;
         // the TMA store that last read this buffer (two stores ago) must be done reading
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
         __syncwarp();
-        for (int g = 0; g < cw; g += 16) {
-          uint32_t v[16];
-          tmem_ld16(t_row + (uint32_t)(c0 + g), v);
-          float f[16];
+        const uint32_t rowaddr = sbuf + (uint32_t)lane * row_bytes;
+        for (int g = 0; g < cw; g += 32) {
+          // two 16-column TMEM loads in flight per wait
+          uint32_t v[2][16];
+          const bool two = g + 16 < cw;
+          tmem_ld16_nowait(t_row + (uint32_t)(c0 + g), v[0]);
+          if (two) tmem_ld16_nowait(t_row + (uint32_t)(c0 + g + 16), v[1]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-          for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]) + __ldg(p.bias + n0 + c0 + g + i);
-          if (rrow) {
-            uint4 r0 = *reinterpret_cast<const uint4*>(rrow + c0 + g);
-            uint4 r1 = *reinterpret_cast<const uint4*>(rrow + c0 + g + 8);
-            const __nv_bfloat16* rb0 = reinterpret_cast<const __nv_bfloat16*>(&r0);
-            const __nv_bfloat16* rb1 = reinterpret_cast<const __nv_bfloat16*>(&r1);
+          for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !two) break;
+            const int gg = g + 16 * h;
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + c0 + gg);
+            float f[16];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              float4 b4 = __ldg(bp + i);
+              f[4 * i + 0] = __uint_as_float(v[h][4 * i + 0]) + b4.x;
+              f[4 * i + 1] = __uint_as_float(v[h][4 * i + 1]) + b4.y;
+              f[4 * i + 2] = __uint_as_float(v[h][4 * i + 2]) + b4.z;
+              f[4 * i + 3] = __uint_as_float(v[h][4 * i + 3]) + b4.w;
+            }
+            const uint32_t j0 = (uint32_t)(gg >> 3);  // 16-byte chunk index of this group inside the row
+            if (p.has_res) {
+              uint32_t rr[8];
+              const uint32_t ra = r_row + (uint32_t)ci * chunk_bytes;
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(rr[0]), "=r"(rr[1]), "=r"(rr[2]), "=r"(rr[3])
+                           : "r"(ra + ((j0 ^ swz) << 4)));
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(rr[4]), "=r"(rr[5]), "=r"(rr[6]), "=r"(rr[7])
+                           : "r"(ra + (((j0 + 1u) ^ swz) << 4)));
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                f[2 * i] += __uint_as_float(rr[i] << 16);             // low bf16 of the pair
+                f[2 * i + 1] += __uint_as_float(rr[i] & 0xffff0000u);  // high bf16
+              }
+            }
+            if (p.relu) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
+            }
+            uint32_t pk[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-              f[i] += __bfloat162float(rb0[i]);
-              f[8 + i] += __bfloat162float(rb1[i]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+              pk[i] = *reinterpret_cast<uint32_t*>(&h2);
             }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + ((j0 ^ swz) << 4)), "r"(pk[0]),
+                         "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
+                         : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((j0 + 1u) ^ swz) << 4)), "r"(pk[4]),
+                         "r"(pk[5]), "r"(pk[6]), "r"(pk[7])
+                         : "memory");
           }
-          if (p.relu) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
-          }
-          uint32_t pk[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
-            pk[i] = *reinterpret_cast<uint32_t*>(&h2);
-          }
-          const uint32_t j0 = (uint32_t)(g >> 3);  // 16-byte chunk index of this group inside the row
-          const uint32_t rowaddr = sbuf + (uint32_t)lane * row_bytes;
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + ((j0 ^ swz) << 4)), "r"(pk[0]), "r"(pk[1]),
-                       "r"(pk[2]), "r"(pk[3])
-                       : "memory");
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((j0 + 1u) ^ swz) << 4)), "r"(pk[4]),
-                       "r"(pk[5]), "r"(pk[6]), "r"(pk[7])
-                       : "memory");
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if (lane == 0) {
-          tma_store_2d(&map_o, sbuf, n0 + c0, m0 + q * 32);
+          tma_store_2d(&map_o, sbuf, n0 + c0, p.out_row0 + m0 + q * 32);
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
       }
-      // every tcgen05.ld of this warp has completed (wait::ld): hand the accumulator back
+      // every tcgen05.ld / residual read of this warp is done: hand both buffers back
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tempty0 + 8u * a);
+      if (lane == 0) {
+        mbar_arrive(tempty0 + 8u * a);
+        if (p.has_res) mbar_arrive(rempty0 + 8u * a);
+      }
     }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
@@ -547,7 +599,10 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
   op.version = tune.version == 1 ? 1 : 2;
   const long long M_cap = (long long)n_capacity * p.ho * p.wo;
   const long long m_tiles_cap = (M_cap + BLOCK_M - 1) / BLOCK_M;
+  op.has_res = op.version == 2 && p.res != nullptr;
   op.bn = op.version == 1 ? pick_bn(p.cout, tune.bn) : pick_bn_v2(p.cout, m_tiles_cap, tune.bn);
+  // two residual tiles of 128 x bn bf16 live in shared memory: keep them at 64 KiB
+  if (op.has_res && tune.bn == 0 && op.bn > 128) op.bn = pick_bn(p.cout, 0);
   if (op.bn == 0) return tc_fail("no N tile for cout = %d (override %d)", p.cout, tune.bn);
   if (p.cin_pad % BLOCK_K) return tc_fail("cin_pad = %d is not a multiple of %d", p.cin_pad, BLOCK_K);
   op.cpb = p.cin_pad / BLOCK_K;
@@ -563,7 +618,8 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
     op.tmem_cols = 32;
     while (op.tmem_cols < op.bn) op.tmem_cols *= 2;
   } else {
-    const int fixed = 1024 /*alignment slack*/ + OUT_STAGING_BYTES + 256 /*barriers*/;
+    const int fixed = 1024 /*alignment slack*/ + OUT_STAGING_BYTES + 256 /*barriers*/ +
+                      (op.has_res ? 2 * BLOCK_M * op.bn * 2 : 0);
     int target = (SMEM_LIMIT - fixed) / stage_bytes;
     if (target > 8) target = 8;
     if (tune.stages > 0 && tune.stages < target) target = tune.stages;
@@ -586,6 +642,16 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (ro != CUDA_SUCCESS)
       return tc_fail("cuTensorMapEncodeTiled(output) failed (%d): cout=%d M=%lld pitch=%d cw=%d", (int)ro, p.cout, M_cap, p.out_pitch, op.cw);
+    op.map_r = op.map_o;
+    if (op.has_res) {
+      cuuint64_t rstr[1] = {(cuuint64_t)p.res_pitch * 2};
+      cuuint32_t rbox[2] = {(cuuint32_t)op.cw, (cuuint32_t)BLOCK_M};
+      ro = g_encode_tiled(&op.map_r, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(p.res), odim, rstr, rbox, oes,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, osw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (ro != CUDA_SUCCESS)
+        return tc_fail("cuTensorMapEncodeTiled(residual) failed (%d): cout=%d M=%lld pitch=%d cw=%d", (int)ro, p.cout, M_cap, p.res_pitch, op.cw);
+    }
   }
 
   // A: NHWC view as (C, W, H, N), im2col mode.  Corner convention as in CUTLASS'
@@ -629,7 +695,11 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.bias = p.bias;
     k.res = reinterpret_cast<const __nv_bfloat16*>(p.res);
     k.M = p.n * p.ho * p.wo;
-    if (k.M > op.m_capacity) return tc_fail("batch of %d images exceeds the planned capacity", p.n);
+    k.has_res = op.has_res ? 1 : 0;
+    k.in_img0 = p.in_img0;
+    k.out_row0 = p.out_row0;
+    if ((p.res != nullptr) != op.has_res) return tc_fail("residual pointer does not match the plan");
+    if (k.out_row0 + k.M > op.m_capacity) return tc_fail("batch of %d images exceeds the planned capacity", p.n);
     k.ho = p.ho; k.wo = p.wo;
     k.stride = p.stride; k.pad_h = p.pad_h; k.pad_w = p.pad_w;
     k.kw = p.kw; k.cpb = op.cpb; k.num_kb = p.kh * p.kw * op.cpb;
@@ -640,7 +710,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.cw = op.cw;
     const int tiles = k.m_tiles * k.n_tiles;
     const int grid = tiles < g_num_sms ? tiles : g_num_sms;
-    conv_tc2_kernel<<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, k);
+    conv_tc2_kernel<<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
     cudaError_t e2 = cudaGetLastError();
     if (e2 != cudaSuccess) return tc_fail("conv_tc2_kernel launch: %s", cudaGetErrorString(e2));
     return 0;
@@ -677,6 +747,11 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     p.in = ws + off_arena + ((size_t)net.bufs[ti.buf].offset * micro_batch + ti.c_off) * 2;
     p.w = wts + op.wpack_off;
     p.out = ws + off_arena + ((size_t)net.bufs[to.buf].offset * micro_batch + to.c_off) * 2;
+    if (op.res >= 0) {
+      const Tensor& tr = net.tensors[op.res];
+      p.res = ws + off_arena + ((size_t)net.bufs[tr.buf].offset * micro_batch + tr.c_off) * 2;
+      p.res_pitch = tr.c_pitch;
+    }
     p.n = micro_batch; p.hi = ti.h; p.wi = ti.w; p.cin = op.cin; p.in_pitch = ti.c_pitch;
     p.ho = to.h; p.wo = to.w; p.cout = op.cout; p.out_pitch = to.c_pitch;
     p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;

@@ -26,6 +26,8 @@ struct TcOpPlan {
   int cw = 0;          // epilogue chunk width (columns per TMA store box)
   int acc_stride = 0;  // TMEM columns between the two accumulators
   int m_capacity = 0;  // rows the output map covers
+  alignas(64) CUtensorMap map_r;  // residual view, same geometry as the output
+  bool has_res = false;
 };
 
 struct TcPlan {

@@ -277,7 +277,7 @@ int dml_create(int device, int model, int max_batch, int micro_batch, int flags,
   e->use_tc = !e->fp32 && (flags & DML_FLAG_NO_TENSOR_CORE) == 0;
   e->keep_all = (flags & DML_FLAG_KEEP_ALL) != 0;
   e->act_bytes = e->fp32 ? 4 : 2;
-  if (micro_batch == 0) micro_batch = 32;
+  if (micro_batch == 0) micro_batch = max_batch;  // whole batch per layer: large launches beat L2-resident waves here
   e->micro_batch = micro_batch < max_batch ? micro_batch : max_batch;
   std::string err;
   if (!dml::build_net(model, e->keep_all, e->fp32 ? 4 : 2, !e->fp32, &e->net, &err)) {

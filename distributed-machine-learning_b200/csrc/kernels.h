@@ -15,6 +15,8 @@ struct ConvParams {
   int ho, wo, cout, out_pitch, res_pitch;
   int kh, kw, stride, pad_h, pad_w, cin_pad;
   int relu;
+  int in_img0 = 0;   // tcgen05 path: first image / first output row of this launch inside the
+  int out_row0 = 0;  // planned tensor maps (the pointers above are already offset for the CUDA-core path)
 };
 
 struct PoolParams {
