@@ -13,7 +13,7 @@ import threading
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "libdml_b200.so")
-SOURCES = ["dml_api.cu", "kernels.cu", "conv_tc.cu", "graph.cc"]
+SOURCES = ["dml_api.cu", "kernels.cu", "conv_tc.cu", "stem_tc.cu", "graph.cc"]
 HEADERS = ["conv_tc.h", "graph.h", "kernels.h", os.path.join("..", "..", "include", "dml_b200.h")]
 
 NVCC_FLAGS = [

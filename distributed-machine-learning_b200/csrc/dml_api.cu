@@ -141,6 +141,9 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
       if (e->use_tc && dml::tc_supported(op)) {
         int rc = dml::launch_conv_tc(e->tc, (int)oi, p, img0, s, &nl);
         if (rc != 0) return fail(DML_ECUDA, "tcgen05 conv launch failed for %s: %s", op.name.c_str(), dml::tc_last_error());
+      } else if (e->use_tc && dml::stem_tc_supported(p)) {
+        if (dml::launch_stem_tc(p, s) != 0) return fail(DML_ECUDA, "stem conv launch failed for %s", op.name.c_str());
+        nl = 1;
       } else {
         dml::launch_conv_naive(p, e->fp32, s);
         nl = 1;
@@ -507,7 +510,7 @@ int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* 
     if (op.kind == dml::OP_CONV) {
       macs = (int64_t)to.h * to.w * op.cout * op.kh * op.kw * op.cin;
       wb = (int64_t)op.cout * op.kh * op.kw * op.cin * (e->fp32 ? 4 : 2) + op.cout * 4;
-      im = (e->use_tc && dml::tc_supported(op)) ? 1 : 0;
+      im = (e->use_tc && (dml::tc_supported(op) || (op.cin == 3 && op.stride == 2))) ? 1 : 0;
     }
   }
   if (name && name_cap > 0) snprintf(name, name_cap, "%s", nm.c_str());
@@ -573,6 +576,11 @@ int dml_conv2d_bf16(int impl, const void* d_in, const void* d_w, const float* d_
   if (impl == 0) {
     dml::launch_conv_naive(p, false, (cudaStream_t)stream);
     CUDA_TRY(cudaGetLastError());
+    return 0;
+  }
+  if (impl == 3) {
+    if (!dml::stem_tc_supported(p)) return fail(DML_EINVAL, "shape is not a C_in = 3 stride-2 stem convolution");
+    if (dml::launch_stem_tc(p, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "stem conv launch failed");
     return 0;
   }
   if (impl != 1 && impl != 2) return fail(DML_EINVAL, "impl must be 0 (CUDA cores), 1 (tcgen05, tile per CTA) or 2 (tcgen05, persistent)");

@@ -45,6 +45,10 @@ void launch_preprocess(const PreParams& p, const float* d_lut, bool fp32_out, cu
 // CUDA-core direct convolution (check mode, debug twin, C=3 stems).
 void launch_conv_naive(const ConvParams& p, bool fp32_act, cudaStream_t s);
 
+// K2: C_in = 3 stem convolution on the tensor cores (bf16 mode).
+bool stem_tc_supported(const ConvParams& p);
+int launch_stem_tc(const ConvParams& p, cudaStream_t s);
+
 // K4 / K5: 3x3 max-pool (zero padding participates, as Keras' ZeroPadding2D does)
 // and 3x3 s1 'same' average pool dividing by the in-bounds tap count.
 void launch_maxpool(const PoolParams& p, bool fp32_act, cudaStream_t s);

@@ -71,11 +71,12 @@ def test_preprocess_ragged_and_empty(engines):
     eng.preprocess(0)  # n = 0 is a no-op, not an error
 
 
-def _conv_case(rng, n, hi, wi, cin, cout, kh, kw, stride, pad_h, pad_w, relu, with_res, in_extra=0, out_extra=0):
+def _conv_case(rng, n, hi, wi, cin, cout, kh, kw, stride, pad_h, pad_w, relu, with_res, in_extra=0, out_extra=0, cin_pad=None):
     import torch
     import torch.nn.functional as F
     dev = torch.device("cuda")
-    in_pitch, cin_pad = cin + in_extra, (cin + 63) // 64 * 64
+    in_pitch = cin + in_extra
+    cin_pad = cin_pad or (cin + 63) // 64 * 64
     ho, wo = (hi + 2 * pad_h - kh) // stride + 1, (wi + 2 * pad_w - kw) // stride + 1
     out_pitch = cout + out_extra
     x = torch.from_numpy(rng.standard_normal((n, hi, wi, in_pitch)).astype(np.float32)).to(dev).bfloat16()
@@ -187,3 +188,16 @@ def test_conv_tcgen05_persistent_tiles(case_id):
     assert (got - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
     if shape[13]:
         assert (out[..., cout:].float() == 7.0).all()
+
+
+@pytest.mark.parametrize("shape", [(3, 224, 224, 3, 64, 7, 7, 2, 3, 3, True, False), (2, 299, 299, 3, 32, 3, 3, 2, 0, 0, True, False),
+                                   (1, 37, 53, 3, 64, 7, 7, 2, 3, 3, True, False)], ids=["resnet", "inception", "ragged"])
+def test_stem_conv_tcgen05(shape):
+    rng = np.random.default_rng(99)
+    case = _conv_case(rng, *shape, cin_pad=3)
+    ref = case["ref"]
+    tol = 2e-2 * max(1.0, ref.abs().max().item())
+    base = _run_conv(0, case)
+    assert (base.float() - ref).abs().max().item() <= tol
+    out = _run_conv(3, case)
+    assert (out.float() - ref).abs().max().item() <= tol
