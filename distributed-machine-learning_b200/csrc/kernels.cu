@@ -233,6 +233,53 @@ __global__ void __launch_bounds__(256) pool_kernel(PoolParams p) {
   *reinterpret_cast<uint4*>(out) = *reinterpret_cast<uint4*>(o);
 }
 
+// K5 fast path (3x3, stride 1, pad 1): one thread per (image, output column, channel
+// group) walks down the rows keeping the last three horizontal 3-tap sums, so each
+// output costs 3 loads instead of 9; divisor = valid rows x valid columns.
+template <typename T>
+__global__ void __launch_bounds__(256) avgpool3_kernel(PoolParams p) {
+  constexpr int V = Vec16<T>::N;
+  const int cg = p.c / V;
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)p.n * p.wi * cg) return;
+  const int g = (int)(idx % cg);
+  const int wo = (int)((idx / cg) % p.wi);
+  const int n = (int)(idx / ((int64_t)cg * p.wi));
+  const T* in = reinterpret_cast<const T*>(p.in) + (int64_t)n * p.hi * p.wi * p.in_pitch + g * V;
+  T* out = reinterpret_cast<T*>(p.out) + (int64_t)n * p.hi * p.wi * p.out_pitch + g * V;
+  const int w0 = wo > 0 ? wo - 1 : 0, w1 = wo < p.wi - 1 ? wo + 1 : p.wi - 1;
+  const float ncols = (float)(w1 - w0 + 1);
+  float h0[V], h1[V], h2[V];  // horizontal sums of rows r-1, r, r+1
+#pragma unroll
+  for (int i = 0; i < V; ++i) h0[i] = h1[i] = h2[i] = 0.f;
+  auto hsum = [&](int r, float (&h)[V]) {
+#pragma unroll
+    for (int i = 0; i < V; ++i) h[i] = 0.f;
+    for (int wi = w0; wi <= w1; ++wi) {
+      uint4 raw = *reinterpret_cast<const uint4*>(in + ((int64_t)r * p.wi + wi) * p.in_pitch);
+      const T* v = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+      for (int i = 0; i < V; ++i) h[i] += to_f(v[i]);
+    }
+  };
+  hsum(0, h1);
+  for (int r = 0; r < p.hi; ++r) {
+    const bool has_next = r + 1 < p.hi;
+    if (has_next) hsum(r + 1, h2);
+    const float nrows = (float)((r > 0) + 1 + has_next);
+    const float inv = 1.f / (nrows * ncols);
+    T o[V];
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      float sum = h1[i] + (r > 0 ? h0[i] : 0.f) + (has_next ? h2[i] : 0.f);
+      o[i] = from_f<T>(sum * inv);
+    }
+    *reinterpret_cast<uint4*>(out + ((int64_t)r * p.wi + wo) * p.out_pitch) = *reinterpret_cast<uint4*>(o);
+#pragma unroll
+    for (int i = 0; i < V; ++i) { h0[i] = h1[i]; h1[i] = h2[i]; }
+  }
+}
+
 // K6: one thread per (image, V-channel group), walks the HxW pixels.
 template <typename T>
 __global__ void __launch_bounds__(256) gap_kernel(const T* __restrict__ in, float* __restrict__ out, int n, int hw, int c,
@@ -258,33 +305,60 @@ __global__ void __launch_bounds__(256) gap_kernel(const T* __restrict__ in, floa
 }
 
 // K7a: logits[img][j] = pooled[img] . W[:, j] + b[j].  Block = 8 images x 128
-// columns; pooled rows staged in shared memory, W read once per 8 images.
+// columns, 8 warps each owning a K slice (W read as float4, 4 columns per lane);
+// the 8 partial sums are reduced through shared memory in a fixed order.
 constexpr int FC_IMGS = 8;
 constexpr int FC_COLS = 128;
-__global__ void __launch_bounds__(FC_COLS) fc_kernel(const float* __restrict__ pooled, const float* __restrict__ w,
-                                                     const float* __restrict__ b, float* __restrict__ logits, int n,
-                                                     int cin) {
-  extern __shared__ float xs[];  // FC_IMGS x cin
+constexpr int FC_WARPS = 8;
+__global__ void __launch_bounds__(FC_WARPS * 32) fc_kernel(const float* __restrict__ pooled, const float* __restrict__ w,
+                                                          const float* __restrict__ b, float* __restrict__ logits, int n,
+                                                          int cin) {
+  extern __shared__ float xs[];  // FC_IMGS x cin, later reused for the partial sums
   const int img0 = blockIdx.x * FC_IMGS;
-  const int col = blockIdx.y * FC_COLS + threadIdx.x;
-  for (int i = threadIdx.x; i < FC_IMGS * cin; i += FC_COLS) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int col = blockIdx.y * FC_COLS + lane * 4;
+  for (int i = threadIdx.x; i < FC_IMGS * cin; i += FC_WARPS * 32) {
     int im = img0 + i / cin;
     xs[i] = im < n ? pooled[(int64_t)im * cin + (i % cin)] : 0.f;
   }
   __syncthreads();
-  if (col >= 1000) return;
-  float acc[FC_IMGS];
-#pragma unroll
-  for (int i = 0; i < FC_IMGS; ++i) acc[i] = 0.f;
-  for (int k = 0; k < cin; ++k) {
-    float wv = w[(int64_t)k * 1000 + col];
-#pragma unroll
-    for (int i = 0; i < FC_IMGS; ++i) acc[i] = fmaf(xs[i * cin + k], wv, acc[i]);
-  }
-  float bv = b[col];
+  float acc[FC_IMGS][4];
 #pragma unroll
   for (int i = 0; i < FC_IMGS; ++i)
-    if (img0 + i < n) logits[(int64_t)(img0 + i) * 1000 + col] = acc[i] + bv;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  const int kslice = cin / FC_WARPS;
+  const int k0 = warp * kslice;
+  if (col < 1000) {
+#pragma unroll 4
+    for (int k = k0; k < k0 + kslice; ++k) {
+      const float4 wv = *reinterpret_cast<const float4*>(w + (int64_t)k * 1000 + col);
+#pragma unroll
+      for (int i = 0; i < FC_IMGS; ++i) {
+        const float x = xs[i * cin + k];
+        acc[i][0] = fmaf(x, wv.x, acc[i][0]);
+        acc[i][1] = fmaf(x, wv.y, acc[i][1]);
+        acc[i][2] = fmaf(x, wv.z, acc[i][2]);
+        acc[i][3] = fmaf(x, wv.w, acc[i][3]);
+      }
+    }
+  }
+  __syncthreads();
+  float* part = xs;  // [warp][img][128]
+#pragma unroll
+  for (int i = 0; i < FC_IMGS; ++i)
+    *reinterpret_cast<float4*>(part + ((warp * FC_IMGS + i) * FC_COLS) + lane * 4) =
+        make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+  __syncthreads();
+  for (int o = threadIdx.x; o < FC_IMGS * FC_COLS; o += FC_WARPS * 32) {
+    const int i = o / FC_COLS, c = o % FC_COLS;
+    const int cc = blockIdx.y * FC_COLS + c;
+    if (cc >= 1000 || img0 + i >= n) continue;
+    float sum = b[cc];
+#pragma unroll
+    for (int wv = 0; wv < FC_WARPS; ++wv) sum += part[(wv * FC_IMGS + i) * FC_COLS + c];
+    logits[(int64_t)(img0 + i) * 1000 + cc] = sum;
+  }
 }
 
 // K7b: softmax over 1000 logits + top-5 (descending prob; ties -> larger index).
@@ -376,7 +450,17 @@ static void launch_pool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
   else pool_kernel<__nv_bfloat16, AVG><<<blocks, 256, 0, s>>>(p);
 }
 void launch_maxpool(const PoolParams& p, bool fp32_act, cudaStream_t s) { launch_pool<false>(p, fp32_act, s); }
-void launch_avgpool(const PoolParams& p, bool fp32_act, cudaStream_t s) { launch_pool<true>(p, fp32_act, s); }
+void launch_avgpool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
+  if (p.k == 3 && p.stride == 1 && p.pad == 1 && p.ho == p.hi && p.wo == p.wi) {
+    int V = fp32_act ? 4 : 8;
+    int64_t total = (int64_t)p.n * p.wi * (p.c / V);
+    unsigned blocks = (unsigned)((total + 255) / 256);
+    if (fp32_act) avgpool3_kernel<float><<<blocks, 256, 0, s>>>(p);
+    else avgpool3_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(p);
+    return;
+  }
+  launch_pool<true>(p, fp32_act, s);
+}
 
 void launch_gap(const void* in, float* out, int n, int hw, int c, int in_pitch, bool fp32_act, cudaStream_t s) {
   int V = fp32_act ? 4 : 8;
@@ -393,7 +477,7 @@ void init_kernels() {
 void launch_fc(const float* pooled, const float* w, const float* b, float* logits, int n, int cin, cudaStream_t s) {
   dim3 grid((unsigned)((n + FC_IMGS - 1) / FC_IMGS), (1000 + FC_COLS - 1) / FC_COLS);
   size_t smem = (size_t)FC_IMGS * cin * sizeof(float);
-  fc_kernel<<<grid, FC_COLS, smem, s>>>(pooled, w, b, logits, n, cin);
+  fc_kernel<<<grid, FC_WARPS * 32, smem, s>>>(pooled, w, b, logits, n, cin);
 }
 
 void launch_softmax_top5(const float* logits, float* probs, int32_t* top_idx, float* top_prob, int n, cudaStream_t s) {

@@ -11,6 +11,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 
 #include "kernels.h"
 
@@ -32,6 +33,7 @@ struct StemParams {
   int tiles_x, tiles_y, total_tiles;
   int patch_h, patch_w, ppitch;  // input patch of one tile, row pitch in elements (even)
   int tmem_cols;
+  int debug;  // bit0: no prefetch, bit1: zero whole patch buffer every tile
 };
 
 __device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -87,7 +89,9 @@ __global__ void __launch_bounds__(STEM_THREADS) stem_tc_kernel(const StemParams 
     const int m = i & 127, k = p.kh * p.segpad + ((i >> 7) << 3);
     *reinterpret_cast<uint4*>(sA + sw_chunk(m, k, 128)) = make_uint4(0, 0, 0, 0);
   }
-  for (int i = tid; i < 64; i += STEM_THREADS) patch[patch_elems + i] = __float2bfloat16(0.f);
+  // the pad columns [patch_w*3, ppitch) and the slack are over-read by the expansion (they meet zero
+  // weights, but a stale NaN bit pattern times zero is still NaN): clear the whole buffer once
+  for (int i = tid; i < patch_elems + 64; i += STEM_THREADS) patch[i] = __float2bfloat16(0.f);
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -100,23 +104,43 @@ __global__ void __launch_bounds__(STEM_THREADS) stem_tc_kernel(const StemParams 
   const int prow = p.patch_w * 3;
   uint32_t phase = 0;
 
+  // Patch rows are fetched into registers one tile ahead, so the global-load latency
+  // hides behind the previous tile's MMA and epilogue.
+  constexpr int MAX_ROWS = 11;  // ceil(patch_h / 2) with patch_h <= 22
+  __nv_bfloat16 pre[MAX_ROWS];
+  auto fetch = [&](int tile) {
+    const int img = tile / tiles_per_img;
+    const int tr = tile - img * tiles_per_img;
+    const int ph0 = 2 * ((tr / p.tiles_x) * TILE_H) - p.pad, pw0 = 2 * ((tr % p.tiles_x) * TILE_W) - p.pad;
+    const __nv_bfloat16* img_in = p.in + (size_t)img * p.hi * p.wi * 3;
+    const int c = tid & 127;
+    const int wi = pw0 + c / 3;
+    const bool col_ok = c < prow && wi >= 0 && wi < p.wi;
+#pragma unroll
+    for (int j = 0; j < MAX_ROWS; ++j) {
+      const int r = (tid >> 7) + 2 * j;
+      const int hi = ph0 + r;
+      pre[j] = __float2bfloat16(0.f);
+      if (col_ok && r < p.patch_h && hi >= 0 && hi < p.hi) pre[j] = img_in[((size_t)hi * p.wi + pw0) * 3 + c];
+    }
+  };
+  if ((int)blockIdx.x < p.total_tiles) fetch(blockIdx.x);
+
   for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
     const int img = tile / tiles_per_img;
     const int tr = tile - img * tiles_per_img;
     const int ty0 = (tr / p.tiles_x) * TILE_H, tx0 = (tr % p.tiles_x) * TILE_W;
-    const int ph0 = 2 * ty0 - p.pad, pw0 = 2 * tx0 - p.pad;  // patch origin in the input
 
-    // 1. input patch -> smem (zeros outside the image = the conv's zero padding); 128 threads per row pair
-    const __nv_bfloat16* img_in = p.in + (size_t)img * p.hi * p.wi * 3;
-    for (int r = tid >> 7; r < p.patch_h; r += STEM_THREADS >> 7) {
-      const int hi = ph0 + r;
+    if (p.debug & 1) fetch(tile);
+    // 1. prefetched input patch -> smem (zeros outside the image = the conv's zero padding)
+    {
       const int c = tid & 127;
       if (c < prow) {
-        const int px = c / 3;
-        const int wi = pw0 + px;
-        __nv_bfloat16 v = __float2bfloat16(0.f);
-        if (hi >= 0 && hi < p.hi && wi >= 0 && wi < p.wi) v = img_in[((size_t)hi * p.wi + pw0) * 3 + c];
-        patch[r * p.ppitch + c] = v;
+#pragma unroll
+        for (int j = 0; j < MAX_ROWS; ++j) {
+          const int r = (tid >> 7) + 2 * j;
+          if (r < p.patch_h) patch[r * p.ppitch + c] = pre[j];
+        }
       }
     }
     __syncthreads();
@@ -153,6 +177,7 @@ __global__ void __launch_bounds__(STEM_THREADS) stem_tc_kernel(const StemParams 
       }
       asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
     }
+    if (!(p.debug & 1) && tile + (int)gridDim.x < p.total_tiles) fetch(tile + gridDim.x);
     // 4. epilogue: warps 0-3 take columns [0, cout/2), warps 4-7 the other half; TMEM lane quarter = warp % 4
     {
       uint32_t done = 0;
@@ -208,7 +233,7 @@ __global__ void __launch_bounds__(STEM_THREADS) stem_tc_kernel(const StemParams 
 
 bool stem_tc_supported(const ConvParams& p) {
   return p.cin == 3 && p.stride == 2 && p.cin_pad == 3 && p.pad_h == p.pad_w && (p.cout == 64 || p.cout == 32) &&
-         p.relu && p.res == nullptr && p.kh * ((p.kw * 3 + 7) / 8 * 8) <= 192 && p.kw * 3 + 32 <= 128;
+         p.relu && p.res == nullptr && p.kh * ((p.kw * 3 + 7) / 8 * 8) <= 192 && (30 + p.kw) * 3 <= 128 && p.kh <= 8;
 }
 
 int launch_stem_tc(const ConvParams& c, cudaStream_t s) {
@@ -244,6 +269,8 @@ int launch_stem_tc(const ConvParams& c, cudaStream_t s) {
   int per_sm = (int)((220 * 1024) / (smem + 1024));
   if (per_sm > 4) per_sm = 4;
   if (per_sm < 1) per_sm = 1;
+  if (const char* e = getenv("DML_STEM_DEBUG")) p.debug = atoi(e);
+  if (const char* e = getenv("DML_STEM_PER_SM")) per_sm = atoi(e);
   int grid = num_sms * per_sm;
   if (grid > p.total_tiles) grid = p.total_tiles;
   stem_tc_kernel<<<grid, STEM_THREADS, smem, s>>>(p);

@@ -121,3 +121,23 @@ def test_folding_stress_fp32(images):
         rel = np.abs(logits - ref_logits).max() / np.abs(ref_logits).max()
         print(f"\n{model} folding_stress fp32: logits rel {rel:.3e}")
         assert rel <= 1e-3
+
+
+@pytest.mark.parametrize("model", ["ResNet50", "InceptionV3"])
+def test_deterministic_and_batch_invariant(model, images):
+    """Same images -> bit-identical logits, run to run and whatever else shares the batch
+    (stale shared memory / buffer contents must never leak into results)."""
+    eng = pkg("engine").Engine(model, max_batch=64)
+    try:
+        sel = images[:48]
+        eng.predict_images(sel)
+        a = eng.logits(48).cpu().numpy().copy()
+        eng.predict_images(images[60:70])
+        eng.predict_images(sel)
+        b = eng.logits(48).cpu().numpy().copy()
+        eng.predict_images(sel[:7])
+        c = eng.logits(7).cpu().numpy().copy()
+    finally:
+        eng.close()
+    assert np.array_equal(a, b)
+    assert np.array_equal(a[:7], c)
