@@ -217,6 +217,9 @@ int check_ready(dml_engine* e, int n) {
 
 extern "C" {
 
+// Internal: lets the other translation units of the library report through dml_last_error().
+int dml_set_error(int code, const char* msg) { return fail(code, "%s", msg); }
+
 const char* dml_last_error(void) { return g_err.c_str(); }
 const char* dml_version(void) { return "dml_b200 0.1 (sm_100a)"; }
 

@@ -158,6 +158,27 @@ int dml_conv2d_bf16(int impl, const void* d_in, const void* d_w, const float* d_
                     int kw, int stride, int pad_h, int pad_w, int cin_pad, int relu, int tile_n, int stages,
                     void* stream);
 
+/* The dense(1000) + softmax + top-5 head with NO device allocation anywhere: no
+ * engine, no workspace.  (No counterpart in the reference: its Keras model owns
+ * all of its memory.)  It is for callers that cannot allocate device memory --
+ * inside a stream capture, on a serving thread that may not take cudaMalloc's
+ * device-wide synchronisation, or inside a process whose GPU memory belongs to
+ * another framework's pool.  The n x 1000 fp32 logits, which dml_forward keeps in
+ * the caller's workspace, live in a fixed array inside the library instead:
+ * DML_HEAD_STATIC_MAX_IMAGES x 1000 floats = 4,096,000 bytes held on every GPU
+ * that loads the library, until the process exits.
+ *   d_pooled [n][cin] fp32 (global-average-pooled features), d_dense_w [cin][1000]
+ *   fp32, d_dense_b [1000]; outputs as in dml_forward (d_probs may be NULL).
+ * Runs on the CURRENT device.  n > DML_HEAD_STATIC_MAX_IMAGES -> DML_ESIZE.
+ * The first call on each device looks up the array's device address and sets a
+ * kernel attribute: make that first call outside any stream capture.  All calls on
+ * a device share the one array (it keeps the previous call's logits; every row a
+ * call reads is rewritten by that call first, nothing needs clearing): two calls
+ * whose kernels can overlap on the GPU (different streams) race -- serialise them. */
+#define DML_HEAD_STATIC_MAX_IMAGES 1024
+int dml_head_static(const float* d_pooled, const float* d_dense_w, const float* d_dense_b, int n, int cin,
+                    float* d_probs, int32_t* d_top5_idx, float* d_top5_prob, void* stream);
+
 int dml_sync(dml_engine* e);
 const char* dml_last_error(void);
 const char* dml_version(void);
