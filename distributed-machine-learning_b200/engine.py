@@ -57,6 +57,10 @@ class Engine:
         self.d_hw = torch.empty((max_batch, 2), dtype=torch.int32, device=dev)
         self.d_xtab = torch.empty((max_batch, S), dtype=torch.int32, device=dev)
         self.d_ytab = torch.empty((max_batch, S), dtype=torch.int32, device=dev)
+        # second slot of inputs/results + a copy stream: H2D of batch i+1 overlaps the kernels of batch i
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self._slots = None
+        self._submitted = 0
         self.d_probs = torch.empty((max_batch, 1000), dtype=torch.float32, device=dev)
         self.d_idx = torch.empty((max_batch, 5), dtype=torch.int32, device=dev)
         self.d_prob = torch.empty((max_batch, 5), dtype=torch.float32, device=dev)
@@ -141,6 +145,73 @@ class Engine:
             self.h_prob[:hb.n].copy_(self.d_prob[:hb.n], non_blocking=True)
         self.stream.synchronize()
         return self.h_idx[:hb.n].numpy(), self.h_prob[:hb.n].numpy()
+
+    # -- pipelined host-buffer path -------------------------------------------
+    def _make_slots(self):
+        torch = _torch()
+        dev = self.d_pixels.device
+        S, mb = self.size, self.max_batch
+        slots = []
+        for k in range(2):
+            sl = {
+                "pixels": self.d_pixels if k == 0 else torch.empty_like(self.d_pixels),
+                "img_off": self.d_off if k == 0 else torch.empty_like(self.d_off),
+                "hw": self.d_hw if k == 0 else torch.empty_like(self.d_hw),
+                "xtab": self.d_xtab if k == 0 else torch.empty_like(self.d_xtab),
+                "ytab": self.d_ytab if k == 0 else torch.empty_like(self.d_ytab),
+                "d_idx": torch.empty((mb, 5), dtype=torch.int32, device=dev),
+                "d_prob": torch.empty((mb, 5), dtype=torch.float32, device=dev),
+                "h_idx": torch.empty((mb, 5), dtype=torch.int32).pin_memory(),
+                "h_prob": torch.empty((mb, 5), dtype=torch.float32).pin_memory(),
+                "copied": torch.cuda.Event(), "done": torch.cuda.Event(), "n": 0, "busy": False,
+            }
+            slots.append(sl)
+        self._slots = slots
+
+    def submit(self, hb: frontend.HostBatch) -> int:
+        """Enqueue one batch (host buffers, ideally pinned): H2D on the copy stream, dml_infer and the
+        D2H of the top-5 on the compute stream.  Returns a ticket for collect().  At most two batches
+        may be in flight; the H2D of a batch overlaps the kernels of the one before it."""
+        torch = _torch()
+        if self._slots is None:
+            self._make_slots()
+        k = self._submitted % 2
+        sl = self._slots[k]
+        if sl["busy"]:
+            raise _lib.DmlError("two batches already in flight: collect() one first")
+        n = hb.n
+        if n > self.max_batch or hb.pixels.size > sl["pixels"].numel():
+            raise _lib.DmlError("batch larger than the engine's staging buffers")
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(sl["done"])  # the slot's previous kernels have consumed its inputs
+            sl["pixels"][:hb.pixels.size].copy_(torch.from_numpy(hb.pixels), non_blocking=True)
+            sl["img_off"][:n].copy_(torch.from_numpy(hb.img_off), non_blocking=True)
+            sl["hw"][:n].copy_(torch.from_numpy(hb.hw), non_blocking=True)
+            sl["xtab"][:n].copy_(torch.from_numpy(hb.xtab), non_blocking=True)
+            sl["ytab"][:n].copy_(torch.from_numpy(hb.ytab), non_blocking=True)
+            sl["copied"].record(self.copy_stream)
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(sl["copied"])
+            _lib.check(self.l.dml_infer(self.h, sl["pixels"].data_ptr(), sl["img_off"].data_ptr(), sl["hw"].data_ptr(),
+                                        sl["xtab"].data_ptr(), sl["ytab"].data_ptr(), n, None, sl["d_idx"].data_ptr(),
+                                        sl["d_prob"].data_ptr(), self.stream.cuda_stream))
+            sl["h_idx"][:n].copy_(sl["d_idx"][:n], non_blocking=True)
+            sl["h_prob"][:n].copy_(sl["d_prob"][:n], non_blocking=True)
+            sl["done"].record(self.stream)
+        sl["n"], sl["busy"] = n, True
+        self._submitted += 1
+        return k
+
+    def collect(self, ticket: int):
+        """Wait for a submitted batch; returns (top5_idx, top5_prob) views of pinned memory, valid until the
+        slot is reused two submits later."""
+        sl = self._slots[ticket]
+        if not sl["busy"]:
+            raise _lib.DmlError("nothing in flight for this ticket")
+        sl["done"].synchronize()
+        sl["busy"] = False
+        n = sl["n"]
+        return sl["h_idx"][:n].numpy(), sl["h_prob"][:n].numpy()
 
     def predict_images(self, images, want_probs: bool = False):
         """uint8 HxWx3 arrays -> (top5_idx [n,5] int32, top5_prob [n,5] fp32[, probs [n,1000]])."""

@@ -52,3 +52,29 @@ def test_output_json_shape_and_bad_files(image_dir, tmp_path):
     assert isinstance(top[0], str) and isinstance(top[1], str) and isinstance(top[2], float)
     assert m.perform_inference_without_async("VGG16", files) == "Invalid model"
     assert m.run_inference_on_ResNet50([]) == {}
+
+
+def test_pipelined_submit_collect_matches_serial(images):
+    """Two batches in flight (H2D overlapping kernels) give the same answers as the serial call."""
+    fe = pkg("frontend")
+    eng = pkg("engine").Engine("ResNet50", max_batch=16)
+    try:
+        chunks = [images[i:i + 16] for i in range(0, 80, 16)]
+        want = [eng.predict_images(c) for c in chunks]
+        hbs = [eng.pin(fe.HostBatch(c, eng.size)) for c in chunks]
+        got, pending = [], None
+        for hb in hbs:
+            t = eng.submit(hb)
+            if pending is not None:
+                i, p = eng.collect(pending)
+                got.append((i.copy(), p.copy()))
+            pending = t
+        i, p = eng.collect(pending)
+        got.append((i.copy(), p.copy()))
+        for (wi, wp), (gi, gp) in zip(want, got):
+            assert np.array_equal(wi, gi) and np.array_equal(wp, gp)
+        with pytest.raises(pkg("_lib").DmlError):
+            eng.submit(hbs[0]); eng.submit(hbs[1]); eng.submit(hbs[2])
+    finally:
+        eng.sync()
+        eng.close()
