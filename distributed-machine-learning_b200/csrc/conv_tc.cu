@@ -20,6 +20,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <string>
 
 namespace dml {
@@ -288,7 +289,13 @@ struct TcV2Params {
   int has_res;      // residual tiles are TMA-loaded into shared memory by the producer warp
   int out_row0;     // first output row of this launch inside the output/residual maps
   int in_img0;      // first image of this launch inside the input map
+  int a_tiled;      // 1x1 stride-1 convs: A is a plain [M][cin] matrix, fetched with tiled TMA
+  int in_row0;      // first input row (pixel) of this launch for the tiled A map
+  int dbg;
 };
+
+// DML_TC_DEBUG=1: per-CTA cycle counters of where each role waits (printed by the launcher)
+__device__ long long g_tc_dbg[256 * 16];
 
 constexpr int OUT_BUF_BYTES = 4096;  // 32 rows x 128 B
 constexpr int OUT_STAGING_BYTES = 4 * 2 * OUT_BUF_BYTES;
@@ -379,10 +386,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
         for (int j = 0; j < p.num_kb; ++j, ++it) {
           const uint32_t s = it % (uint32_t)stages;
           const uint32_t ph = (it / (uint32_t)stages) & 1u;
+          long long t0 = p.dbg ? clock64() : 0;
           mbar_wait(empty0 + 8u * s, ph ^ 1u);
+          if (p.dbg) g_tc_dbg[blockIdx.x * 16 + 0] += clock64() - t0;
           mbar_arrive_expect_tx(full0 + 8u * s, tx_bytes);
-          tma_load_im2col_4d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base,
-                             img + p.in_img0, (uint16_t)sx, (uint16_t)r);
+          if (p.a_tiled)
+            tma_load_2d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, p.in_row0 + m0);
+          else
+            tma_load_im2col_4d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base,
+                               img + p.in_img0, (uint16_t)sx, (uint16_t)r);
           tma_load_2d(sB + s * b_stage_bytes, &map_b, full0 + 8u * s, j * BLOCK_K, n0);
           if (++cb == p.cpb) {
             cb = 0;
@@ -399,14 +411,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
       uint32_t it = 0, lt = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
         const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
-        mbar_wait(tempty0 + 8u * a, aph ^ 1u);  // epilogue has drained this accumulator
+        long long t0 = p.dbg ? clock64() : 0;
+        if (!(p.dbg & 2)) mbar_wait(tempty0 + 8u * a, aph ^ 1u);  // epilogue has drained this accumulator
+        if (p.dbg) g_tc_dbg[blockIdx.x * 16 + 1] += clock64() - t0;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
         for (int j = 0; j < p.num_kb; ++j, ++it) {
           const uint32_t s = it % (uint32_t)stages;
           const uint32_t ph = (it / (uint32_t)stages) & 1u;
+          long long t1 = p.dbg ? clock64() : 0;
           mbar_wait(full0 + 8u * s, ph);
+          if (p.dbg) g_tc_dbg[blockIdx.x * 16 + 2] += clock64() - t1;
           tc_fence_after();
+          if (p.dbg & 2) {  // feed-rate experiment: consume the stage without any tensor-core work
+            mbar_arrive(empty0 + 8u * s);
+            continue;
+          }
           const uint64_t da = make_sw128_desc(sA + s * A_STAGE_BYTES);
           const uint64_t db = make_sw128_desc(sB + s * b_stage_bytes);
 #pragma unroll
@@ -414,7 +434,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
             umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((j | k) != 0));
           umma_commit(empty0 + 8u * s);
         }
-        umma_commit(tfull0 + 8u * a);
+        if (!(p.dbg & 2)) umma_commit(tfull0 + 8u * a);
       }
     }
   } else {
@@ -426,12 +446,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
     const uint32_t chunk_bytes = (uint32_t)BLOCK_M * row_bytes;
     const uint32_t swz = cw == 64 ? (uint32_t)(lane & 7) : (cw == 32 ? (uint32_t)((lane >> 1) & 3) : (uint32_t)((lane >> 2) & 1));
     uint32_t lt = 0, nstore = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+    for (int tile = blockIdx.x; tile < total_tiles && !(p.dbg & 2); tile += gridDim.x, ++lt) {
       const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
       const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
       const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+      const bool dbg = p.dbg && warp == 2 && lane == 0;
+      long long t0 = dbg ? clock64() : 0;
       if (p.has_res) mbar_wait(rfull0 + 8u * a, aph);
+      if (dbg) { long long t = clock64(); g_tc_dbg[blockIdx.x * 16 + 3] += t - t0; t0 = t; }
       mbar_wait(tfull0 + 8u * a, aph);
+      if (dbg) { long long t = clock64(); g_tc_dbg[blockIdx.x * 16 + 4] += t - t0; t0 = t; }
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
       const uint32_t r_row = sR + a * res_tile_bytes + (uint32_t)(q * 32 + lane) * row_bytes;
@@ -439,8 +463,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
       for (int c0 = 0; c0 < p.bn; c0 += cw, ++nstore, ++ci) {
         const uint32_t sbuf = my_out + (nstore & 1u) * OUT_BUF_BYTES;
         // the TMA store that last read this buffer (two stores ago) must be done reading
+        long long t2 = dbg ? clock64() : 0;
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
         __syncwarp();
+        if (dbg) g_tc_dbg[blockIdx.x * 16 + 5] += clock64() - t2;
         const uint32_t rowaddr = sbuf + (uint32_t)lane * row_bytes;
         for (int g = 0; g < cw; g += 32) {
           // two 16-column TMEM loads in flight per wait
@@ -511,6 +537,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
         mbar_arrive(tempty0 + 8u * a);
         if (p.has_res) mbar_arrive(rempty0 + 8u * a);
       }
+      if (dbg) { g_tc_dbg[blockIdx.x * 16 + 6] += clock64() - t0; g_tc_dbg[blockIdx.x * 16 + 7] += 1; }
     }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
@@ -662,7 +689,20 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
   int lower[2] = {-p.pad_w, -p.pad_h};
   int upper[2] = {p.pad_w - (p.kw - 1), p.pad_h - (p.kh - 1)};
   cuuint32_t estr[4] = {1, (cuuint32_t)p.stride, (cuuint32_t)p.stride, 1};
-  CUresult r = g_encode_im2col(&op.map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p.in), gdim, gstr, lower,
+  op.a_tiled = op.version == 2 && p.kh == 1 && p.kw == 1 && p.stride == 1 && p.pad_h == 0 && p.pad_w == 0 &&
+               !getenv("DML_NO_TILED_A");
+  CUresult r = CUDA_SUCCESS;
+  if (op.a_tiled) {
+    cuuint64_t adim[2] = {(cuuint64_t)p.cin, (cuuint64_t)n_capacity * p.hi * p.wi};
+    cuuint64_t astr[1] = {(cuuint64_t)p.in_pitch * 2};
+    cuuint32_t abox[2] = {BLOCK_K, BLOCK_M};
+    cuuint32_t aes[2] = {1, 1};
+    r = g_encode_tiled(&op.map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(p.in), adim, astr, abox, aes,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return tc_fail("cuTensorMapEncodeTiled(A) failed (%d)", (int)r);
+  } else
+  r = g_encode_im2col(&op.map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p.in), gdim, gstr, lower,
                                upper, BLOCK_K, BLOCK_M, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
@@ -697,6 +737,8 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.M = p.n * p.ho * p.wo;
     k.has_res = op.has_res ? 1 : 0;
     k.in_img0 = p.in_img0;
+    k.a_tiled = op.a_tiled ? 1 : 0;
+    k.in_row0 = p.in_img0 * p.hi * p.wi;
     k.out_row0 = p.out_row0;
     if ((p.res != nullptr) != op.has_res) return tc_fail("residual pointer does not match the plan");
     if (k.out_row0 + k.M > op.m_capacity) return tc_fail("batch of %d images exceeds the planned capacity", p.n);
@@ -710,7 +752,27 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.cw = op.cw;
     const int tiles = k.m_tiles * k.n_tiles;
     const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+    static const char* dbg_str = getenv("DML_TC_DEBUG");
+    static const int dbg_val = dbg_str ? atoi(dbg_str) : 0;
+    const bool dbg_env = (dbg_val & 1) != 0;
+    k.dbg = dbg_val;
+    if (dbg_env) {
+      static long long zeros[256 * 16] = {};
+      cudaMemcpyToSymbol(g_tc_dbg, zeros, sizeof zeros);
+    }
     conv_tc2_kernel<<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
+    if (dbg_env) {
+      static long long host[256 * 16];
+      cudaDeviceSynchronize();
+      cudaMemcpyFromSymbol(host, g_tc_dbg, sizeof host);
+      double acc[8] = {};
+      for (int b = 0; b < grid; ++b) for (int i = 0; i < 8; ++i) acc[i] += (double)host[b * 16 + i];
+      double tiles_cta = acc[7] / grid;
+      fprintf(stderr, "[tc dbg] grid %d bn %d kb %d stages %d tiles/cta %.1f | per tile cycles: prod wait empty %.0f, mma wait tempty %.0f, "
+                      "mma wait full %.0f, epi wait res %.0f, epi wait tfull %.0f, epi wait store-read %.0f, epi work %.0f\n",
+              grid, op.bn, k.num_kb, op.stages, tiles_cta, acc[0] / acc[7], acc[1] / acc[7], acc[2] / acc[7], acc[3] / acc[7],
+              acc[4] / acc[7], acc[5] / acc[7], acc[6] / acc[7]);
+    }
     cudaError_t e2 = cudaGetLastError();
     if (e2 != cudaSuccess) return tc_fail("conv_tc2_kernel launch: %s", cudaGetErrorString(e2));
     return 0;

@@ -28,6 +28,7 @@ struct TcOpPlan {
   int m_capacity = 0;  // rows the output map covers
   alignas(64) CUtensorMap map_r;  // residual view, same geometry as the output
   bool has_res = false;
+  bool a_tiled = false;  // A fetched with a tiled 2D map (1x1 stride-1 convs)
 };
 
 struct TcPlan {
