@@ -366,7 +366,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
       const uint32_t tx_bytes = A_STAGE_BYTES + b_stage_bytes;
       uint32_t it = 0, lt = 0;
       const uint32_t chunk_bytes = (uint32_t)BLOCK_M * (uint32_t)p.cw * 2u;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      for (int tile = blockIdx.x; tile < total_tiles && !(p.dbg & 8); tile += gridDim.x, ++lt) {
         const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
         const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
         if (p.has_res) {
@@ -386,9 +386,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
         for (int j = 0; j < p.num_kb; ++j, ++it) {
           const uint32_t s = it % (uint32_t)stages;
           const uint32_t ph = (it / (uint32_t)stages) & 1u;
-          long long t0 = p.dbg ? clock64() : 0;
+          long long t0 = (p.dbg & 1) ? clock64() : 0;
           mbar_wait(empty0 + 8u * s, ph ^ 1u);
-          if (p.dbg) g_tc_dbg[blockIdx.x * 16 + 0] += clock64() - t0;
+          if (p.dbg & 1) g_tc_dbg[blockIdx.x * 16 + 0] += clock64() - t0;
           mbar_arrive_expect_tx(full0 + 8u * s, tx_bytes);
           if (p.a_tiled)
             tma_load_2d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, p.in_row0 + m0);
@@ -411,17 +411,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
       uint32_t it = 0, lt = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
         const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
-        long long t0 = p.dbg ? clock64() : 0;
+        long long t0 = (p.dbg & 1) ? clock64() : 0;
         if (!(p.dbg & 2)) mbar_wait(tempty0 + 8u * a, aph ^ 1u);  // epilogue has drained this accumulator
-        if (p.dbg) g_tc_dbg[blockIdx.x * 16 + 1] += clock64() - t0;
+        if (p.dbg & 1) g_tc_dbg[blockIdx.x * 16 + 1] += clock64() - t0;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
         for (int j = 0; j < p.num_kb; ++j, ++it) {
           const uint32_t s = it % (uint32_t)stages;
           const uint32_t ph = (it / (uint32_t)stages) & 1u;
-          long long t1 = p.dbg ? clock64() : 0;
-          mbar_wait(full0 + 8u * s, ph);
-          if (p.dbg) g_tc_dbg[blockIdx.x * 16 + 2] += clock64() - t1;
+          long long t1 = (p.dbg & 1) ? clock64() : 0;
+          if (!(p.dbg & 8)) mbar_wait(full0 + 8u * s, ph);
+          if (p.dbg & 1) g_tc_dbg[blockIdx.x * 16 + 2] += clock64() - t1;
           tc_fence_after();
           if (p.dbg & 2) {  // feed-rate experiment: consume the stage without any tensor-core work
             mbar_arrive(empty0 + 8u * s);
@@ -430,9 +430,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
           const uint64_t da = make_sw128_desc(sA + s * A_STAGE_BYTES);
           const uint64_t db = make_sw128_desc(sB + s * b_stage_bytes);
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k)
-            umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((j | k) != 0));
-          umma_commit(empty0 + 8u * s);
+          for (int k = 0; k < BLOCK_K / 16; ++k) {
+            // dbg bit 2 (timing experiment only, results are wrong): four independent accumulators
+            const uint32_t dd = (p.dbg & 4) ? tmem_base + (uint32_t)(k * p.bn) : d_tmem;
+            umma_bf16(dd, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((j | k) != 0));
+          }
+          // dbg bit 3: MMA-only experiment (operands are whatever is in smem); bit 4 adds a commit per k-block
+          if (!(p.dbg & 8)) umma_commit(empty0 + 8u * s);
+          else if (p.dbg & 16) umma_commit(rempty0);
         }
         if (!(p.dbg & 2)) umma_commit(tfull0 + 8u * a);
       }
@@ -450,7 +455,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
       const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
       const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
       const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
-      const bool dbg = p.dbg && warp == 2 && lane == 0;
+      const bool dbg = (p.dbg & 1) && warp == 2 && lane == 0;
       long long t0 = dbg ? clock64() : 0;
       if (p.has_res) mbar_wait(rfull0 + 8u * a, aph);
       if (dbg) { long long t = clock64(); g_tc_dbg[blockIdx.x * 16 + 3] += t - t0; t0 = t; }
@@ -549,6 +554,238 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
   }
 }
 
+
+// ------------- v3: stride-1 multi-tap convs with the input halo staged ONCE -------------
+// im2col through L2 re-reads every input pixel once per filter tap (9x for 3x3) and the
+// L2 -> SM path (~6 TB/s, no faster than HBM) is what bounds those layers.  Here a tile is
+// 128 consecutive positions q of one image's PADDED raster (q = hp*Wp + wp, Wp = W + 2*pad_w).
+// The producer loads the rows that cover [q, q + 128 + (kh-1)*Wp + kw-1) with one tiled TMA box
+// per 64-channel block (zero fill outside the image = the conv's padding); the A operand of tap
+// (r, s) is then the SAME shared memory seen through a descriptor that starts (r*Wp + s) pixels
+// (128 bytes each) later.  Positions with wp >= Wo or hp >= Ho are computed and dropped.
+struct TcV3Params {
+  const float* bias;
+  __nv_bfloat16* out;
+  int n_img, ho, wo, wp, out_pitch;
+  int kh, kw, pad_h, pad_w, cblocks;
+  int tiles_per_img, q_valid;   // positions [0, q_valid) of an image hold all its outputs
+  int rows_box;                 // input rows per TMA box
+  int a_stage_bytes, a_stages, b_stages;
+  int bn, n_tiles, relu;
+  int tmem_cols, acc_stride, cw;
+  int in_img0, out_img0;
+  int desc_mode;                // experiment: how the unaligned A start is described
+};
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_constant__ CUtensorMap map_a,
+                                                                 const __grid_constant__ CUtensorMap map_b,
+                                                                 const TcV3Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t b_stage_bytes = (uint32_t)p.bn * 128u;
+  const uint32_t sA = base;
+  const uint32_t sB = sA + (uint32_t)p.a_stages * (uint32_t)p.a_stage_bytes;
+  const uint32_t sO = sB + (uint32_t)p.b_stages * b_stage_bytes;      // 2 x [128 rows][128 B] staging
+  const uint32_t sOff = sO + 2u * 16384u;                              // 2 x 128 int32 output offsets
+  const uint32_t bars = sOff + 1024u;
+  const uint32_t afull0 = bars, aempty0 = afull0 + 8u * p.a_stages;
+  const uint32_t bfull0 = aempty0 + 8u * p.a_stages, bempty0 = bfull0 + 8u * p.b_stages;
+  const uint32_t tfull0 = bempty0 + 8u * p.b_stages, tempty0 = tfull0 + 16u;
+  const uint32_t tmem_slot = tempty0 + 16u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int taps = p.kh * p.kw;
+  const int total_tiles = p.n_img * p.tiles_per_img * p.n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    for (int i = 0; i < p.a_stages; ++i) { mbar_init(afull0 + 8u * i, 1); mbar_init(aempty0 + 8u * i, 1); }
+    for (int i = 0; i < p.b_stages; ++i) { mbar_init(bfull0 + 8u * i, 1); mbar_init(bempty0 + 8u * i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(tfull0 + 8u * i, 1); mbar_init(tempty0 + 8u * i, 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(p.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  // tile -> (image, first position, n tile); N tiles of one position range are adjacent
+  auto decode = [&](int tile, int& img, int& l0, int& n0) {
+    const int nt = tile % p.n_tiles;
+    const int mt = tile / p.n_tiles;
+    img = mt / p.tiles_per_img;
+    l0 = (mt - img * p.tiles_per_img) * BLOCK_M;
+    n0 = nt * p.bn;
+  };
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---------------- producer: one halo box per channel block, one weight tile per (block, tap) ----------------
+      uint32_t ita = 0, itb = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int img, l0, n0;
+        decode(tile, img, l0, n0);
+        const int row0 = l0 / p.wp;  // first padded row the tile touches
+        for (int cb = 0; cb < p.cblocks; ++cb, ++ita) {
+          const uint32_t sa = ita % (uint32_t)p.a_stages, pha = (ita / (uint32_t)p.a_stages) & 1u;
+          mbar_wait(aempty0 + 8u * sa, pha ^ 1u);
+          mbar_arrive_expect_tx(afull0 + 8u * sa, (uint32_t)p.rows_box * (uint32_t)p.wp * 128u);
+          // 4D tiled box {64 ch, Wp, rows_box, 1} at (channel, -pad_w, row0 - pad_h, image): OOB -> zeros
+          asm volatile(
+              "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+                  sA + sa * (uint32_t)p.a_stage_bytes),
+              "l"(&map_a), "r"(afull0 + 8u * sa), "r"(cb * BLOCK_K), "r"(-p.pad_w), "r"(row0 - p.pad_h), "r"(img + p.in_img0)
+              : "memory");
+          for (int t = 0; t < taps; ++t, ++itb) {
+            const uint32_t sb = itb % (uint32_t)p.b_stages, phb = (itb / (uint32_t)p.b_stages) & 1u;
+            mbar_wait(bempty0 + 8u * sb, phb ^ 1u);
+            mbar_arrive_expect_tx(bfull0 + 8u * sb, b_stage_bytes);
+            tma_load_2d(sB + sb * b_stage_bytes, &map_b, bfull0 + 8u * sb, (t * p.cblocks + cb) * BLOCK_K, n0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ---------------- MMA issuer ----------------
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+      uint32_t ita = 0, itb = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+        int img, l0, n0;
+        decode(tile, img, l0, n0);
+        const int loff = l0 - (l0 / p.wp) * p.wp;  // tile's first position inside the loaded rows
+        const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+        mbar_wait(tempty0 + 8u * a, aph ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
+        uint32_t first = 1;
+        for (int cb = 0; cb < p.cblocks; ++cb, ++ita) {
+          const uint32_t sa = ita % (uint32_t)p.a_stages, pha = (ita / (uint32_t)p.a_stages) & 1u;
+          mbar_wait(afull0 + 8u * sa, pha);
+          tc_fence_after();
+          const uint32_t a_base = sA + sa * (uint32_t)p.a_stage_bytes;
+          int r = 0, sx = 0;
+          for (int t = 0; t < taps; ++t, ++itb) {
+            const uint32_t sb = itb % (uint32_t)p.b_stages, phb = (itb / (uint32_t)p.b_stages) & 1u;
+            mbar_wait(bfull0 + 8u * sb, phb);
+            tc_fence_after();
+            const uint32_t a_addr = a_base + (uint32_t)(loff + r * p.wp + sx) * 128u;
+            // the swizzle is a function of the absolute shared-memory address, so a start that is only
+            // 128-byte aligned needs no base_offset (checked on B200: base_offset = (addr >> 7) & 7 is wrong)
+            const uint64_t da = make_sw128_desc(a_addr);
+            const uint64_t db = make_sw128_desc(sB + sb * b_stage_bytes);
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / 16; ++k) {
+              umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, first ? 0u : 1u);
+              first = 0;
+            }
+            umma_commit(bempty0 + 8u * sb);
+            if (++sx == p.kw) { sx = 0; ++r; }
+          }
+          umma_commit(aempty0 + 8u * sa);
+        }
+        umma_commit(tfull0 + 8u * a);
+      }
+    }
+  } else {
+    // ---------------- epilogue: 4 warps = 128 positions; staged in smem, written with coalesced 16-byte stores ----------------
+    const int q = warp & 3;
+    const int et = q * 32 + lane;  // epilogue thread id = tile row
+    const int cw = p.cw;
+    const int chunks16 = cw >> 3;  // 16-byte pieces per staged row
+    uint32_t lt = 0, nchunk = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      int img, l0, n0;
+      decode(tile, img, l0, n0);
+      const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+      // output offset of this thread's position (elements), -1 if the position is padding
+      {
+        const int pos = l0 + et;
+        const int hp = pos / p.wp, wq = pos - hp * p.wp;
+        int off = -1;
+        if (hp < p.ho && wq < p.wo) off = (((img + p.out_img0) * p.ho + hp) * p.wo + wq) * p.out_pitch + n0;
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(sOff + (lt & 1u) * 512u + (uint32_t)et * 4u), "r"(off) : "memory");
+      }
+      mbar_wait(tfull0 + 8u * a, aph);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
+      for (int c0 = 0; c0 < p.bn; c0 += cw, ++nchunk) {
+        const uint32_t sbuf = sO + (nchunk & 1u) * 16384u;
+        const uint32_t rowaddr = sbuf + (uint32_t)et * 128u;
+        const uint32_t swz = (uint32_t)(et & 7);
+        for (int g = 0; g < cw; g += 32) {
+          uint32_t v[2][16];
+          const bool two = g + 16 < cw;
+          tmem_ld16_nowait(t_row + (uint32_t)(c0 + g), v[0]);
+          if (two) tmem_ld16_nowait(t_row + (uint32_t)(c0 + g + 16), v[1]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !two) break;
+            const int gg = g + 16 * h;
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + c0 + gg);
+            uint32_t pk[8];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              float4 b4 = __ldg(bp + i);
+              float f0 = __uint_as_float(v[h][4 * i + 0]) + b4.x, f1 = __uint_as_float(v[h][4 * i + 1]) + b4.y;
+              float f2 = __uint_as_float(v[h][4 * i + 2]) + b4.z, f3 = __uint_as_float(v[h][4 * i + 3]) + b4.w;
+              if (p.relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); f2 = fmaxf(f2, 0.f); f3 = fmaxf(f3, 0.f); }
+              __nv_bfloat162 lo = __floats2bfloat162_rn(f0, f1), hi = __floats2bfloat162_rn(f2, f3);
+              pk[2 * i] = *reinterpret_cast<uint32_t*>(&lo);
+              pk[2 * i + 1] = *reinterpret_cast<uint32_t*>(&hi);
+            }
+            const uint32_t j0 = (uint32_t)(gg >> 3);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + ((j0 ^ swz) << 4)), "r"(pk[0]),
+                         "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
+                         : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((j0 + 1u) ^ swz) << 4)), "r"(pk[4]),
+                         "r"(pk[5]), "r"(pk[6]), "r"(pk[7])
+                         : "memory");
+          }
+        }
+        named_bar_sync(1, 128);  // the whole 128 x cw chunk (and the offset table) is staged
+        // cooperative copy-out: consecutive threads take consecutive 16-byte pieces of a row
+        for (int idx = et; idx < BLOCK_M * chunks16; idx += 128) {
+          const int m = idx / chunks16, j = idx - m * chunks16;
+          int off;
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(off) : "r"(sOff + (lt & 1u) * 512u + (uint32_t)m * 4u) : "memory");
+          if (off >= 0) {
+            uint4 val;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(val.x), "=r"(val.y), "=r"(val.z), "=r"(val.w)
+                         : "r"(sbuf + (uint32_t)m * 128u + (((uint32_t)j ^ (uint32_t)(m & 7)) << 4))
+                         : "memory");
+            *reinterpret_cast<uint4*>(p.out + off + c0 + j * 8) = val;
+          }
+        }
+        // the other staging buffer is free again once everybody left the copy-out two chunks ago:
+        // the bar.sync of the NEXT chunk orders that (each buffer is reused every second chunk)
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty0 + 8u * a);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+  }
+}
+
 }  // namespace
 
 // ------------------------------- host side ---------------------------------
@@ -610,6 +847,8 @@ int tc_init() {
   }
   cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(conv_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc3_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc2_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   int dev = 0, sms = 0;
@@ -623,6 +862,69 @@ size_t tc_scratch_bytes(const Net&, int) { return 0; }
 int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune& tune) {
   if (!g_encode_tiled) return tc_fail("tc_init was not called");
   TcOpPlan op;
+  // ---- v3: halo kernel for stride-1 multi-tap convs whose Cin is a multiple of 64 ----
+  {
+    const bool eligible = p.stride == 1 && p.kh * p.kw > 1 && p.cin % BLOCK_K == 0 && p.cin_pad == p.cin && p.res == nullptr &&
+                          p.wi + 2 * p.pad_w <= 256 && p.out != nullptr;
+    const int wp = p.wi + 2 * p.pad_w;
+    const int q_valid = (p.ho - 1) * wp + p.wo;
+    const int tiles_img = (q_valid + BLOCK_M - 1) / BLOCK_M;
+    const double eff = (double)p.ho * p.wo / ((double)tiles_img * BLOCK_M);
+    const bool want = tune.version == 3 || (tune.version == 0 && eff >= 0.70 && !getenv("DML_NO_V3"));
+    if (tune.version == 3 && !eligible) return tc_fail("shape is not eligible for the halo kernel");
+    if (eligible && want) {
+      op.version = 3;
+      op.wp = wp; op.q_valid = q_valid; op.tiles_per_img = tiles_img;
+      const int halo = (p.kh - 1) * wp + p.kw - 1;
+      op.rows_box = (wp - 1 + BLOCK_M - 1 + halo) / wp + 1;
+      if (op.rows_box > 256) return tc_fail("halo box too tall");
+      op.a_stage_bytes = (op.rows_box * wp * 128 + 1023) / 1024 * 1024;
+      op.cpb = p.cin / BLOCK_K;
+      const long long m_tiles = (long long)n_capacity * tiles_img;
+      op.bn = pick_bn_v2(p.cout, m_tiles, tune.bn);
+      if (op.bn == 0) return tc_fail("no N tile for cout = %d", p.cout);
+      op.acc_stride = 32;
+      while (op.acc_stride < op.bn) op.acc_stride *= 2;
+      op.tmem_cols = 2 * op.acc_stride;
+      op.cw = op.bn % 64 == 0 ? 64 : (op.bn % 32 == 0 ? 32 : 16);
+      const int fixed = 1024 + 2 * 16384 + 1024 + 512;
+      op.a_stages = op.cpb >= 2 ? 3 : 2;
+      if (const char* e = getenv("DML_V3_ASTAGES")) op.a_stages = atoi(e);
+      int b_bytes = op.bn * 128;
+      while (op.a_stages > 1 && fixed + op.a_stages * op.a_stage_bytes + 2 * b_bytes > SMEM_LIMIT) --op.a_stages;
+      int room = SMEM_LIMIT - fixed - op.a_stages * op.a_stage_bytes;
+      op.b_stages = room / b_bytes;
+      if (op.b_stages > 12) op.b_stages = 12;
+      if (tune.stages > 0 && tune.stages < op.b_stages) op.b_stages = tune.stages;
+      if (op.b_stages >= 2) {
+        op.smem = (size_t)fixed + (size_t)op.a_stages * op.a_stage_bytes + (size_t)op.b_stages * b_bytes;
+        op.m_capacity = n_capacity;
+        static const char* dm = getenv("DML_V3_DESC_MODE");
+        op.desc_mode = dm ? atoi(dm) : 0;
+        cuuint64_t gdim[4] = {(cuuint64_t)p.cin, (cuuint64_t)p.wi, (cuuint64_t)p.hi, (cuuint64_t)n_capacity};
+        cuuint64_t gstr[3] = {(cuuint64_t)p.in_pitch * 2, (cuuint64_t)p.wi * p.in_pitch * 2, (cuuint64_t)p.hi * p.wi * p.in_pitch * 2};
+        cuuint32_t box[4] = {BLOCK_K, (cuuint32_t)wp, (cuuint32_t)op.rows_box, 1};
+        cuuint32_t es[4] = {1, 1, 1, 1};
+        CUresult r3 = g_encode_tiled(&op.map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p.in), gdim, gstr, box, es,
+                                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r3 != CUDA_SUCCESS) return tc_fail("cuTensorMapEncodeTiled(halo A) failed (%d): wp=%d rows=%d", (int)r3, wp, op.rows_box);
+        const cuuint64_t ktot = (cuuint64_t)p.kh * p.kw * p.cin_pad;
+        cuuint64_t bdim[2] = {ktot, (cuuint64_t)p.cout};
+        cuuint64_t bstr[1] = {ktot * 2};
+        cuuint32_t bbox[2] = {BLOCK_K, (cuuint32_t)op.bn};
+        cuuint32_t bes[2] = {1, 1};
+        r3 = g_encode_tiled(&op.map_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(p.w), bdim, bstr, bbox, bes,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r3 != CUDA_SUCCESS) return tc_fail("cuTensorMapEncodeTiled(weights) failed (%d)", (int)r3);
+        op.valid = true;
+        *out = op;
+        return 0;
+      }
+      if (tune.version == 3) return tc_fail("halo kernel does not fit in shared memory for this shape");
+    }
+  }
   op.version = tune.version == 1 ? 1 : 2;
   const long long M_cap = (long long)n_capacity * p.ho * p.wo;
   const long long m_tiles_cap = (M_cap + BLOCK_M - 1) / BLOCK_M;
@@ -730,6 +1032,26 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
 
 int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s) {
   if (!op.valid) return tc_fail("conv plan is not valid");
+  if (op.version == 3) {
+    TcV3Params k{};
+    k.bias = p.bias;
+    k.out = reinterpret_cast<__nv_bfloat16*>(p.out);
+    k.n_img = p.n; k.ho = p.ho; k.wo = p.wo; k.wp = op.wp; k.out_pitch = p.out_pitch;
+    k.kh = p.kh; k.kw = p.kw; k.pad_h = p.pad_h; k.pad_w = p.pad_w; k.cblocks = op.cpb;
+    k.tiles_per_img = op.tiles_per_img; k.q_valid = op.q_valid; k.rows_box = op.rows_box;
+    k.a_stage_bytes = op.a_stage_bytes; k.a_stages = op.a_stages; k.b_stages = op.b_stages;
+    k.bn = op.bn; k.n_tiles = p.cout / op.bn; k.relu = p.relu;
+    k.tmem_cols = op.tmem_cols; k.acc_stride = op.acc_stride; k.cw = op.cw;
+    k.in_img0 = p.in_img0; k.out_img0 = 0;  // p.out already points at the launch's first image
+    k.desc_mode = op.desc_mode;
+    if (p.in_img0 + p.n > op.m_capacity) return tc_fail("batch of %d images exceeds the planned capacity", p.n);
+    const long long tiles = (long long)p.n * op.tiles_per_img * k.n_tiles;
+    const int grid = tiles < g_num_sms ? (int)tiles : g_num_sms;
+    conv_tc3_kernel<<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+    cudaError_t e3 = cudaGetLastError();
+    if (e3 != cudaSuccess) return tc_fail("conv_tc3_kernel launch: %s", cudaGetErrorString(e3));
+    return 0;
+  }
   if (op.version == 2) {
     TcV2Params k{};
     k.bias = p.bias;
@@ -756,6 +1078,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     static const int dbg_val = dbg_str ? atoi(dbg_str) : 0;
     const bool dbg_env = (dbg_val & 1) != 0;
     k.dbg = dbg_val;
+    if (dbg_val & 4) k.tmem_cols = 512;
     if (dbg_env) {
       static long long zeros[256 * 16] = {};
       cudaMemcpyToSymbol(g_tc_dbg, zeros, sizeof zeros);

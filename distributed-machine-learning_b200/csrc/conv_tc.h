@@ -29,6 +29,9 @@ struct TcOpPlan {
   alignas(64) CUtensorMap map_r;  // residual view, same geometry as the output
   bool has_res = false;
   bool a_tiled = false;  // A fetched with a tiled 2D map (1x1 stride-1 convs)
+  // v3 (halo kernel)
+  int wp = 0, rows_box = 0, tiles_per_img = 0, q_valid = 0, a_stage_bytes = 0, a_stages = 0, b_stages = 0;
+  int desc_mode = 0;
 };
 
 struct TcPlan {
@@ -40,7 +43,7 @@ struct TcPlan {
 struct TcTune {
   int bn = 0;
   int stages = 0;
-  int version = 0;  // 1 = one tile per CTA, 2 = persistent (default)
+  int version = 0;  // 1 = one tile per CTA, 2 = persistent im2col, 3 = halo kernel; 0 = choose
 };
 
 bool tc_supported(const Op& op);

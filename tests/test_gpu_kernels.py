@@ -201,3 +201,33 @@ def test_stem_conv_tcgen05(shape):
     assert (base.float() - ref).abs().max().item() <= tol
     out = _run_conv(3, case)
     assert (out.float() - ref).abs().max().item() <= tol
+
+
+HALO_CASES = [
+    # n, hi, wi, cin, cout, kh, kw, stride, pad_h, pad_w, relu, res, in_extra, out_extra ; tile_n, stages
+    ((2, 56, 56, 64, 64, 3, 3, 1, 1, 1, True, False, 0, 0), 0, 0),
+    ((5, 56, 56, 64, 64, 3, 3, 1, 1, 1, True, False, 0, 0), 32, 3),
+    ((3, 28, 28, 128, 128, 3, 3, 1, 1, 1, True, False, 0, 0), 0, 0),
+    ((9, 28, 28, 128, 128, 3, 3, 1, 1, 1, False, False, 0, 0), 64, 0),
+    ((4, 14, 14, 256, 256, 3, 3, 1, 1, 1, True, False, 0, 0), 0, 0),
+    ((2, 35, 35, 64, 96, 3, 3, 1, 0, 0, True, False, 0, 160), 0, 0),      # valid conv, concat-slice store, 32-column chunks
+    ((2, 35, 35, 64, 64, 5, 5, 1, 2, 2, True, False, 0, 32), 0, 0),       # 5x5 same
+    ((3, 17, 17, 128, 192, 1, 7, 1, 0, 3, True, False, 0, 0), 0, 0),      # 1x7
+    ((3, 17, 17, 192, 192, 7, 1, 1, 3, 0, True, False, 576, 0), 0, 0),    # 7x1, input is a channel slice
+    ((1, 147, 147, 64, 64, 3, 3, 1, 1, 1, True, False, 0, 0), 0, 0),      # rows wider than one tile
+    ((2, 8, 8, 384, 384, 1, 3, 1, 0, 1, True, False, 0, 1664), 0, 0),
+]
+
+
+@pytest.mark.parametrize("case_id", range(len(HALO_CASES)))
+def test_conv_tcgen05_halo_kernel(case_id):
+    shape, tile_n, stages = HALO_CASES[case_id]
+    rng = np.random.default_rng(4321 + case_id)
+    case = _conv_case(rng, *shape)
+    out = _run_conv(4, case, tile_n, stages)
+    cout = shape[4]
+    ref = case["ref"]
+    got = out[..., :cout].float()
+    assert (got - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
+    if shape[13]:
+        assert (out[..., cout:].float() == 7.0).all()
