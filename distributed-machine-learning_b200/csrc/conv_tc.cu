@@ -786,6 +786,278 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_co
   }
 }
 
+
+// ------------- v4: the persistent kernel on CTA PAIRS (tcgen05 cta_group::2, M = 256) -------------
+// One tcgen05.mma costs ~150-250 cycles of tensor-pipe time on B200 however little it computes
+// (measured: MMA-only runs), so a 128 x N x 16 instruction cannot reach peak.  Two CTAs of a
+// cluster (one SM pair) therefore share each instruction: every CTA loads its own 128 rows of A and
+// HALF of the weight tile, the leader CTA issues tcgen05.mma.cta_group::2 (M = 256, N = bn) and both
+// CTAs receive their 128 accumulator rows in their own TMEM.  Twice the work per instruction, and a
+// third less operand traffic per output.
+constexpr uint32_t PEER_BIT_MASK = 0xFEFFFFFFu;  // shared::cluster address -> same offset in the pair's even CTA
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma2_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int x, int y) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar & PEER_BIT_MASK), "r"(x), "r"(y)
+      : "memory");
+}
+__device__ __forceinline__ void tma2_load_im2col_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c, int w, int h,
+                                                    int n, uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
+      "l"(map), "r"(bar & PEER_BIT_MASK), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+__device__ __forceinline__ void umma2_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void umma2_commit_both(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & PEER_BIT_MASK) : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
+    conv_tc2x_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                     const __grid_constant__ CUtensorMap map_o, const __grid_constant__ CUtensorMap map_r,
+                     const TcV2Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int stages = p.stages;
+  const uint32_t b_half_bytes = (uint32_t)p.bn * 64u;  // bn/2 weight rows of 128 bytes
+  const uint32_t sA = base;
+  const uint32_t sB = sA + (uint32_t)stages * A_STAGE_BYTES;
+  const uint32_t sO = sB + (uint32_t)stages * b_half_bytes;
+  const uint32_t res_tile_bytes = p.has_res ? (uint32_t)BLOCK_M * (uint32_t)p.bn * 2u : 0u;
+  const uint32_t sR = sO + OUT_STAGING_BYTES;
+  const uint32_t bars = sR + 2u * res_tile_bytes;
+  const uint32_t full0 = bars, empty0 = bars + 8u * stages;
+  const uint32_t tfull0 = bars + 16u * stages, tempty0 = tfull0 + 16u;
+  const uint32_t rfull0 = tempty0 + 16u, rempty0 = rfull0 + 16u;
+  const uint32_t tmem_slot = rempty0 + 16u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+  const int total_tiles = p.m_tiles * p.n_tiles;  // m_tiles counts 256-row tiles here
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_o) : "memory");
+    for (int i = 0; i < stages; ++i) {
+      mbar_init(full0 + 8u * i, 1);   // leader: its own arrive.expect_tx covers the bytes of both CTAs
+      mbar_init(empty0 + 8u * i, 1);  // one multicast commit per stage
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(tfull0 + 8u * i, 1);
+      mbar_init(tempty0 + 8u * i, 8);  // leader: 4 epilogue warps of each CTA
+      mbar_init(rfull0 + 8u * i, 1);
+      mbar_init(rempty0 + 8u * i, 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(p.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // both CTAs' barriers exist before anything remote touches them
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---------------- TMA producer (both CTAs): own 128 A rows, own half of the weight tile ----------------
+      const int howo = p.ho * p.wo;
+      const uint32_t tx_bytes = 2u * A_STAGE_BYTES + 2u * b_half_bytes;
+      uint32_t it = 0, lt = 0;
+      const uint32_t chunk_bytes = (uint32_t)BLOCK_M * (uint32_t)p.cw * 2u;
+      for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
+        const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
+        const int m0 = mt * 2 * BLOCK_M + (int)rank * BLOCK_M, n0 = nt * p.bn;
+        if (p.has_res) {
+          const uint32_t rb = lt & 1u, rph = (lt >> 1) & 1u;
+          mbar_wait(rempty0 + 8u * rb, rph ^ 1u);
+          mbar_arrive_expect_tx(rfull0 + 8u * rb, res_tile_bytes);
+          for (int c = 0, ci = 0; c < p.bn; c += p.cw, ++ci)
+            tma_load_2d(sR + rb * res_tile_bytes + (uint32_t)ci * chunk_bytes, &map_r, rfull0 + 8u * rb, n0 + c,
+                        p.out_row0 + m0);
+        }
+        const int img = m0 / howo;
+        const int rem = m0 - img * howo;
+        const int oh = rem / p.wo, ow = rem - oh * p.wo;
+        const int w_base = ow * p.stride - p.pad_w, h_base = oh * p.stride - p.pad_h;
+        int cb = 0, r = 0, sx = 0;
+        for (int j = 0; j < p.num_kb; ++j, ++it) {
+          const uint32_t s = it % (uint32_t)stages;
+          const uint32_t ph = (it / (uint32_t)stages) & 1u;
+          mbar_wait(empty0 + 8u * s, ph ^ 1u);
+          if (leader) mbar_arrive_expect_tx(full0 + 8u * s, tx_bytes);
+          if (p.a_tiled)
+            tma2_load_2d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, p.in_row0 + m0);
+          else
+            tma2_load_im2col_4d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base,
+                                img + p.in_img0, (uint16_t)sx, (uint16_t)r);
+          tma2_load_2d(sB + s * b_half_bytes, &map_b, full0 + 8u * s, j * BLOCK_K, n0 + (int)rank * (p.bn >> 1));
+          if (++cb == p.cpb) {
+            cb = 0;
+            if (++sx == p.kw) { sx = 0; ++r; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && leader) {
+      // ---------------- MMA issuer (leader CTA only) ----------------
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)((2 * BLOCK_M) >> 4) << 24);
+      uint32_t it = 0, lt = 0;
+      for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
+        const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+        mbar_wait(tempty0 + 8u * a, aph ^ 1u);  // both CTAs' epilogues have drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
+        for (int j = 0; j < p.num_kb; ++j, ++it) {
+          const uint32_t s = it % (uint32_t)stages;
+          const uint32_t ph = (it / (uint32_t)stages) & 1u;
+          mbar_wait(full0 + 8u * s, ph);
+          tc_fence_after();
+          const uint64_t da = make_sw128_desc(sA + s * A_STAGE_BYTES);
+          const uint64_t db = make_sw128_desc(sB + s * b_half_bytes);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k)
+            umma2_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((j | k) != 0));
+          umma2_commit_both(empty0 + 8u * s);  // frees the stage in BOTH CTAs
+        }
+        umma2_commit_both(tfull0 + 8u * a);
+      }
+    }
+  } else {
+    // ---------------- epilogue warps (both CTAs, own 128 rows) ----------------
+    const int q = warp & 3;
+    const uint32_t my_out = sO + (uint32_t)q * 2u * OUT_BUF_BYTES;
+    const int cw = p.cw;
+    const uint32_t row_bytes = (uint32_t)cw * 2u;
+    const uint32_t chunk_bytes = (uint32_t)BLOCK_M * row_bytes;
+    const uint32_t swz = cw == 64 ? (uint32_t)(lane & 7) : (cw == 32 ? (uint32_t)((lane >> 1) & 3) : (uint32_t)((lane >> 2) & 1));
+    uint32_t lt = 0, nstore = 0;
+    for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
+      const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
+      const int m0 = mt * 2 * BLOCK_M + (int)rank * BLOCK_M, n0 = nt * p.bn;
+      const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+      if (p.has_res) mbar_wait(rfull0 + 8u * a, aph);
+      mbar_wait(tfull0 + 8u * a, aph);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
+      const uint32_t r_row = sR + a * res_tile_bytes + (uint32_t)(q * 32 + lane) * row_bytes;
+      int ci = 0;
+      for (int c0 = 0; c0 < p.bn; c0 += cw, ++nstore, ++ci) {
+        const uint32_t sbuf = my_out + (nstore & 1u) * OUT_BUF_BYTES;
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        __syncwarp();
+        const uint32_t rowaddr = sbuf + (uint32_t)lane * row_bytes;
+        for (int g = 0; g < cw; g += 32) {
+          uint32_t v[2][16];
+          const bool two = g + 16 < cw;
+          tmem_ld16_nowait(t_row + (uint32_t)(c0 + g), v[0]);
+          if (two) tmem_ld16_nowait(t_row + (uint32_t)(c0 + g + 16), v[1]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !two) break;
+            const int gg = g + 16 * h;
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + c0 + gg);
+            float f[16];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              float4 b4 = __ldg(bp + i);
+              f[4 * i + 0] = __uint_as_float(v[h][4 * i + 0]) + b4.x;
+              f[4 * i + 1] = __uint_as_float(v[h][4 * i + 1]) + b4.y;
+              f[4 * i + 2] = __uint_as_float(v[h][4 * i + 2]) + b4.z;
+              f[4 * i + 3] = __uint_as_float(v[h][4 * i + 3]) + b4.w;
+            }
+            const uint32_t j0 = (uint32_t)(gg >> 3);
+            if (p.has_res) {
+              uint32_t rr[8];
+              const uint32_t ra = r_row + (uint32_t)ci * chunk_bytes;
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(rr[0]), "=r"(rr[1]), "=r"(rr[2]), "=r"(rr[3])
+                           : "r"(ra + ((j0 ^ swz) << 4)));
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(rr[4]), "=r"(rr[5]), "=r"(rr[6]), "=r"(rr[7])
+                           : "r"(ra + (((j0 + 1u) ^ swz) << 4)));
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                f[2 * i] += __uint_as_float(rr[i] << 16);
+                f[2 * i + 1] += __uint_as_float(rr[i] & 0xffff0000u);
+              }
+            }
+            if (p.relu) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
+            }
+            uint32_t pk[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+              pk[i] = *reinterpret_cast<uint32_t*>(&h2);
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + ((j0 ^ swz) << 4)), "r"(pk[0]),
+                         "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
+                         : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((j0 + 1u) ^ swz) << 4)), "r"(pk[4]),
+                         "r"(pk[5]), "r"(pk[6]), "r"(pk[7])
+                         : "memory");
+          }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&map_o, sbuf, n0 + c0, p.out_row0 + m0 + q * 32);
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive_leader(tempty0 + 8u * a);  // the leader's MMA warp waits for both CTAs
+        if (p.has_res) mbar_arrive(rempty0 + 8u * a);
+      }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // the peer may still be reading/arriving on this CTA's memory
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+  }
+}
+
 }  // namespace
 
 // ------------------------------- host side ---------------------------------
@@ -849,6 +1121,8 @@ int tc_init() {
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc3_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(conv_tc2x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc2x_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc2_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   int dev = 0, sms = 0;
@@ -925,18 +1199,19 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
       if (tune.version == 3) return tc_fail("halo kernel does not fit in shared memory for this shape");
     }
   }
-  op.version = tune.version == 1 ? 1 : 2;
+  op.version = tune.version == 1 ? 1 : (tune.version == 4 ? 4 : 2);
+  const bool pair = op.version == 4;  // CTA pairs: 256-row tiles, each CTA stages half of the weight tile
   const long long M_cap = (long long)n_capacity * p.ho * p.wo;
-  const long long m_tiles_cap = (M_cap + BLOCK_M - 1) / BLOCK_M;
-  op.has_res = op.version == 2 && p.res != nullptr;
-  op.bn = op.version == 1 ? pick_bn(p.cout, tune.bn) : pick_bn_v2(p.cout, m_tiles_cap, tune.bn);
+  const long long m_tiles_cap = pair ? (M_cap + 2 * BLOCK_M - 1) / (2 * BLOCK_M) : (M_cap + BLOCK_M - 1) / BLOCK_M;
+  op.has_res = op.version != 1 && p.res != nullptr;
+  op.bn = op.version == 1 ? pick_bn(p.cout, tune.bn) : pick_bn_v2(p.cout, pair ? 2 * m_tiles_cap : m_tiles_cap, tune.bn);
   // two residual tiles of 128 x bn bf16 live in shared memory: keep them at 64 KiB
   if (op.has_res && tune.bn == 0 && op.bn > 128) op.bn = pick_bn(p.cout, 0);
   if (op.bn == 0) return tc_fail("no N tile for cout = %d (override %d)", p.cout, tune.bn);
   if (p.cin_pad % BLOCK_K) return tc_fail("cin_pad = %d is not a multiple of %d", p.cin_pad, BLOCK_K);
   op.cpb = p.cin_pad / BLOCK_K;
   const int num_kb = p.kh * p.kw * op.cpb;
-  const int stage_bytes = A_STAGE_BYTES + op.bn * 128;
+  const int stage_bytes = A_STAGE_BYTES + (pair ? op.bn * 64 : op.bn * 128);
   if (op.version == 1) {
     int target = op.bn <= 64 ? 3 : (op.bn <= 128 ? 3 : 4);
     if (tune.stages > 0) target = tune.stages;
@@ -991,7 +1266,7 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
   int lower[2] = {-p.pad_w, -p.pad_h};
   int upper[2] = {p.pad_w - (p.kw - 1), p.pad_h - (p.kh - 1)};
   cuuint32_t estr[4] = {1, (cuuint32_t)p.stride, (cuuint32_t)p.stride, 1};
-  op.a_tiled = op.version == 2 && p.kh == 1 && p.kw == 1 && p.stride == 1 && p.pad_h == 0 && p.pad_w == 0 &&
+  op.a_tiled = op.version != 1 && p.kh == 1 && p.kw == 1 && p.stride == 1 && p.pad_h == 0 && p.pad_w == 0 &&
                !getenv("DML_NO_TILED_A");
   CUresult r = CUDA_SUCCESS;
   if (op.a_tiled) {
@@ -1018,7 +1293,7 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
   const cuuint64_t ktot = (cuuint64_t)p.kh * p.kw * p.cin_pad;
   cuuint64_t bdim[2] = {ktot, (cuuint64_t)p.cout};
   cuuint64_t bstr[1] = {ktot * 2};
-  cuuint32_t bbox[2] = {BLOCK_K, (cuuint32_t)op.bn};
+  cuuint32_t bbox[2] = {BLOCK_K, (cuuint32_t)(pair ? op.bn / 2 : op.bn)};
   cuuint32_t bes[2] = {1, 1};
   r = g_encode_tiled(&op.map_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(p.w), bdim, bstr, bbox, bes,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -1052,7 +1327,8 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     if (e3 != cudaSuccess) return tc_fail("conv_tc3_kernel launch: %s", cudaGetErrorString(e3));
     return 0;
   }
-  if (op.version == 2) {
+  if (op.version == 2 || op.version == 4) {
+    const bool pair = op.version == 4;
     TcV2Params k{};
     k.bias = p.bias;
     k.res = reinterpret_cast<const __nv_bfloat16*>(p.res);
@@ -1069,7 +1345,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.kw = p.kw; k.cpb = op.cpb; k.num_kb = p.kh * p.kw * op.cpb;
     k.bn = op.bn; k.res_pitch = p.res_pitch; k.relu = p.relu;
     k.stages = op.stages; k.tmem_cols = op.tmem_cols; k.acc_stride = op.acc_stride;
-    k.m_tiles = (k.M + BLOCK_M - 1) / BLOCK_M;
+    k.m_tiles = pair ? (k.M + 2 * BLOCK_M - 1) / (2 * BLOCK_M) : (k.M + BLOCK_M - 1) / BLOCK_M;
     k.n_tiles = p.cout / op.bn;
     k.cw = op.cw;
     const int tiles = k.m_tiles * k.n_tiles;
@@ -1083,6 +1359,10 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
       static long long zeros[256 * 16] = {};
       cudaMemcpyToSymbol(g_tc_dbg, zeros, sizeof zeros);
     }
+    if (pair) {
+      const int clusters = tiles < g_num_sms / 2 ? tiles : g_num_sms / 2;
+      conv_tc2x_kernel<<<2 * clusters, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
+    } else
     conv_tc2_kernel<<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
     if (dbg_env) {
       static long long host[256 * 16];

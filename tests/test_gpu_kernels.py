@@ -231,3 +231,30 @@ def test_conv_tcgen05_halo_kernel(case_id):
     assert (got - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
     if shape[13]:
         assert (out[..., cout:].float() == 7.0).all()
+
+
+PAIR_CASES = [
+    ((8, 56, 56, 64, 256, 1, 1, 1, 0, 0, True, True, 0, 0), 0, 0),      # 1x1 + residual, tiled A
+    ((8, 56, 56, 64, 256, 1, 1, 1, 0, 0, True, False, 0, 0), 256, 0),
+    ((3, 56, 56, 256, 128, 1, 1, 2, 0, 0, True, False, 0, 0), 0, 0),     # stride-2 1x1 (im2col)
+    ((16, 28, 28, 128, 128, 3, 3, 1, 1, 1, True, False, 0, 0), 0, 0),
+    ((5, 7, 7, 512, 512, 3, 3, 1, 1, 1, True, False, 0, 0), 0, 2),       # odd tile count, 2 stages
+    ((32, 14, 14, 1024, 256, 1, 1, 1, 0, 0, True, False, 0, 0), 0, 0),
+    ((9, 35, 35, 64, 96, 3, 3, 1, 1, 1, True, False, 0, 160), 0, 0),     # bn 96, concat slice
+    ((2, 17, 17, 160, 192, 7, 1, 1, 3, 0, True, False, 0, 576), 0, 0),
+    ((1, 5, 5, 64, 32, 1, 1, 1, 0, 0, False, False, 0, 0), 0, 0),        # one partial tile: peer CTA has no rows
+]
+
+
+@pytest.mark.parametrize("case_id", range(len(PAIR_CASES)))
+def test_conv_tcgen05_cta_pair(case_id):
+    shape, tile_n, stages = PAIR_CASES[case_id]
+    rng = np.random.default_rng(777 + case_id)
+    case = _conv_case(rng, *shape)
+    out = _run_conv(5, case, tile_n, stages)
+    cout = shape[4]
+    ref = case["ref"]
+    got = out[..., :cout].float()
+    assert (got - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
+    if shape[13]:
+        assert (out[..., cout:].float() == 7.0).all()
