@@ -94,6 +94,13 @@ __device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const CUtensorM
       "l"(map), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
       : "memory");
 }
+// One lane of a converged warp; the rest of the loop stays warp-uniform so that addresses and
+// descriptors live in uniform registers (no per-instruction R2UR / serialisation loop).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
@@ -291,11 +298,8 @@ struct TcV2Params {
   int in_img0;      // first image of this launch inside the input map
   int a_tiled;      // 1x1 stride-1 convs: A is a plain [M][cin] matrix, fetched with tiled TMA
   int in_row0;      // first input row (pixel) of this launch for the tiled A map
-  int dbg;
+  int last_kmma;    // K=16 steps that carry real channels in the last 64-channel block of a tap (1..4)
 };
-
-// DML_TC_DEBUG=1: per-CTA cycle counters of where each role waits (printed by the launcher)
-__device__ long long g_tc_dbg[256 * 16];
 
 constexpr int OUT_BUF_BYTES = 4096;  // 32 rows x 128 B
 constexpr int OUT_STAGING_BYTES = 4 * 2 * OUT_BUF_BYTES;
@@ -360,35 +364,36 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
   if (warp == 0) {
-    if (lane == 0) {
-      // ---------------- TMA producer ----------------
-      const int howo = p.ho * p.wo;
-      const uint32_t tx_bytes = A_STAGE_BYTES + b_stage_bytes;
-      uint32_t it = 0, lt = 0;
-      const uint32_t chunk_bytes = (uint32_t)BLOCK_M * (uint32_t)p.cw * 2u;
-      for (int tile = blockIdx.x; tile < total_tiles && !(p.dbg & 8); tile += gridDim.x, ++lt) {
-        const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
-        const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
-        if (p.has_res) {
-          // whole residual tile of this output tile, one box per column chunk
-          const uint32_t rb = lt & 1u, rph = (lt >> 1) & 1u;
-          mbar_wait(rempty0 + 8u * rb, rph ^ 1u);
+    // ---------------- TMA producer (whole warp walks the loop, one elected lane issues) ----------------
+    const int howo = p.ho * p.wo;
+    const uint32_t tx_bytes = A_STAGE_BYTES + b_stage_bytes;
+    uint32_t it = 0, lt = 0;
+    const uint32_t chunk_bytes = (uint32_t)BLOCK_M * (uint32_t)p.cw * 2u;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
+      const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
+      if (p.has_res) {
+        // whole residual tile of this output tile, one box per column chunk
+        const uint32_t rb = lt & 1u, rph = (lt >> 1) & 1u;
+        mbar_wait(rempty0 + 8u * rb, rph ^ 1u);
+        if (elect_one()) {
           mbar_arrive_expect_tx(rfull0 + 8u * rb, res_tile_bytes);
           for (int c = 0, ci = 0; c < p.bn; c += p.cw, ++ci)
             tma_load_2d(sR + rb * res_tile_bytes + (uint32_t)ci * chunk_bytes, &map_r, rfull0 + 8u * rb, n0 + c,
                         p.out_row0 + m0);
         }
-        const int img = m0 / howo;
-        const int rem = m0 - img * howo;
-        const int oh = rem / p.wo, ow = rem - oh * p.wo;
-        const int w_base = ow * p.stride - p.pad_w, h_base = oh * p.stride - p.pad_h;
-        int tap = 0, cb = 0, r = 0, sx = 0;
-        for (int j = 0; j < p.num_kb; ++j, ++it) {
-          const uint32_t s = it % (uint32_t)stages;
-          const uint32_t ph = (it / (uint32_t)stages) & 1u;
-          long long t0 = (p.dbg & 1) ? clock64() : 0;
-          mbar_wait(empty0 + 8u * s, ph ^ 1u);
-          if (p.dbg & 1) g_tc_dbg[blockIdx.x * 16 + 0] += clock64() - t0;
+        __syncwarp();
+      }
+      const int img = m0 / howo;
+      const int rem = m0 - img * howo;
+      const int oh = rem / p.wo, ow = rem - oh * p.wo;
+      const int w_base = ow * p.stride - p.pad_w, h_base = oh * p.stride - p.pad_h;
+      int cb = 0, r = 0, sx = 0;
+      for (int j = 0; j < p.num_kb; ++j, ++it) {
+        const uint32_t s = it % (uint32_t)stages;
+        const uint32_t ph = (it / (uint32_t)stages) & 1u;
+        mbar_wait(empty0 + 8u * s, ph ^ 1u);
+        if (elect_one()) {
           mbar_arrive_expect_tx(full0 + 8u * s, tx_bytes);
           if (p.a_tiled)
             tma_load_2d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, p.in_row0 + m0);
@@ -396,51 +401,44 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
             tma_load_im2col_4d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base,
                                img + p.in_img0, (uint16_t)sx, (uint16_t)r);
           tma_load_2d(sB + s * b_stage_bytes, &map_b, full0 + 8u * s, j * BLOCK_K, n0);
-          if (++cb == p.cpb) {
-            cb = 0;
-            ++tap;
-            if (++sx == p.kw) { sx = 0; ++r; }
-          }
+        }
+        __syncwarp();
+        if (++cb == p.cpb) {
+          cb = 0;
+          if (++sx == p.kw) { sx = 0; ++r; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ---------------- MMA issuer ----------------
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
-      uint32_t it = 0, lt = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-        const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
-        long long t0 = (p.dbg & 1) ? clock64() : 0;
-        if (!(p.dbg & 2)) mbar_wait(tempty0 + 8u * a, aph ^ 1u);  // epilogue has drained this accumulator
-        if (p.dbg & 1) g_tc_dbg[blockIdx.x * 16 + 1] += clock64() - t0;
+    // ---------------- MMA issuer (whole warp walks the loop, one elected lane issues) ----------------
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+    uint32_t it = 0, lt = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+      mbar_wait(tempty0 + 8u * a, aph ^ 1u);  // epilogue has drained this accumulator
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
+      int cb = 0;
+      for (int j = 0; j < p.num_kb; ++j, ++it) {
+        const uint32_t s = it % (uint32_t)stages;
+        const uint32_t ph = (it / (uint32_t)stages) & 1u;
+        mbar_wait(full0 + 8u * s, ph);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
-        for (int j = 0; j < p.num_kb; ++j, ++it) {
-          const uint32_t s = it % (uint32_t)stages;
-          const uint32_t ph = (it / (uint32_t)stages) & 1u;
-          long long t1 = (p.dbg & 1) ? clock64() : 0;
-          if (!(p.dbg & 8)) mbar_wait(full0 + 8u * s, ph);
-          if (p.dbg & 1) g_tc_dbg[blockIdx.x * 16 + 2] += clock64() - t1;
-          tc_fence_after();
-          if (p.dbg & 2) {  // feed-rate experiment: consume the stage without any tensor-core work
-            mbar_arrive(empty0 + 8u * s);
-            continue;
-          }
-          const uint64_t da = make_sw128_desc(sA + s * A_STAGE_BYTES);
-          const uint64_t db = make_sw128_desc(sB + s * b_stage_bytes);
+        const uint64_t da = make_sw128_desc(sA + s * A_STAGE_BYTES);
+        const uint64_t db = make_sw128_desc(sB + s * b_stage_bytes);
+        // channels past Cin in the last block of a tap are zero padding: skip their K steps
+        const int nk = (cb == p.cpb - 1) ? p.last_kmma : BLOCK_K / 16;
+        if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k) {
-            // dbg bit 2 (timing experiment only, results are wrong): four independent accumulators
-            const uint32_t dd = (p.dbg & 4) ? tmem_base + (uint32_t)(k * p.bn) : d_tmem;
-            umma_bf16(dd, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((j | k) != 0));
-          }
-          // dbg bit 3: MMA-only experiment (operands are whatever is in smem); bit 4 adds a commit per k-block
-          if (!(p.dbg & 8)) umma_commit(empty0 + 8u * s);
-          else if (p.dbg & 16) umma_commit(rempty0);
+          for (int k = 0; k < BLOCK_K / 16; ++k)
+            if (k < nk) umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((j | k) != 0));
+          umma_commit(empty0 + 8u * s);
         }
-        if (!(p.dbg & 2)) umma_commit(tfull0 + 8u * a);
+        __syncwarp();
+        if (++cb == p.cpb) cb = 0;
       }
+      if (elect_one()) umma_commit(tfull0 + 8u * a);
+      __syncwarp();
     }
   } else {
     // ---------------- epilogue warps ----------------
@@ -451,16 +449,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
     const uint32_t chunk_bytes = (uint32_t)BLOCK_M * row_bytes;
     const uint32_t swz = cw == 64 ? (uint32_t)(lane & 7) : (cw == 32 ? (uint32_t)((lane >> 1) & 3) : (uint32_t)((lane >> 2) & 1));
     uint32_t lt = 0, nstore = 0;
-    for (int tile = blockIdx.x; tile < total_tiles && !(p.dbg & 2); tile += gridDim.x, ++lt) {
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
       const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
       const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
-      const bool dbg = (p.dbg & 1) && warp == 2 && lane == 0;
-      long long t0 = dbg ? clock64() : 0;
       if (p.has_res) mbar_wait(rfull0 + 8u * a, aph);
-      if (dbg) { long long t = clock64(); g_tc_dbg[blockIdx.x * 16 + 3] += t - t0; t0 = t; }
       mbar_wait(tfull0 + 8u * a, aph);
-      if (dbg) { long long t = clock64(); g_tc_dbg[blockIdx.x * 16 + 4] += t - t0; t0 = t; }
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
       const uint32_t r_row = sR + a * res_tile_bytes + (uint32_t)(q * 32 + lane) * row_bytes;
@@ -468,10 +462,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
       for (int c0 = 0; c0 < p.bn; c0 += cw, ++nstore, ++ci) {
         const uint32_t sbuf = my_out + (nstore & 1u) * OUT_BUF_BYTES;
         // the TMA store that last read this buffer (two stores ago) must be done reading
-        long long t2 = dbg ? clock64() : 0;
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
         __syncwarp();
-        if (dbg) g_tc_dbg[blockIdx.x * 16 + 5] += clock64() - t2;
         const uint32_t rowaddr = sbuf + (uint32_t)lane * row_bytes;
         for (int g = 0; g < cw; g += 32) {
           // two 16-column TMEM loads in flight per wait
@@ -542,7 +534,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
         mbar_arrive(tempty0 + 8u * a);
         if (p.has_res) mbar_arrive(rempty0 + 8u * a);
       }
-      if (dbg) { g_tc_dbg[blockIdx.x * 16 + 6] += clock64() - t0; g_tc_dbg[blockIdx.x * 16 + 7] += 1; }
     }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
@@ -630,16 +621,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_co
   };
 
   if (warp == 0) {
-    if (lane == 0) {
-      // ---------------- producer: one halo box per channel block, one weight tile per (block, tap) ----------------
-      uint32_t ita = 0, itb = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        int img, l0, n0;
-        decode(tile, img, l0, n0);
-        const int row0 = l0 / p.wp;  // first padded row the tile touches
-        for (int cb = 0; cb < p.cblocks; ++cb, ++ita) {
-          const uint32_t sa = ita % (uint32_t)p.a_stages, pha = (ita / (uint32_t)p.a_stages) & 1u;
-          mbar_wait(aempty0 + 8u * sa, pha ^ 1u);
+    // ---------------- producer: one halo box per channel block, one weight tile per (block, tap) ----------------
+    uint32_t ita = 0, itb = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int img, l0, n0;
+      decode(tile, img, l0, n0);
+      const int row0 = l0 / p.wp;  // first padded row the tile touches
+      for (int cb = 0; cb < p.cblocks; ++cb, ++ita) {
+        const uint32_t sa = ita % (uint32_t)p.a_stages, pha = (ita / (uint32_t)p.a_stages) & 1u;
+        mbar_wait(aempty0 + 8u * sa, pha ^ 1u);
+        if (elect_one()) {
           mbar_arrive_expect_tx(afull0 + 8u * sa, (uint32_t)p.rows_box * (uint32_t)p.wp * 128u);
           // 4D tiled box {64 ch, Wp, rows_box, 1} at (channel, -pad_w, row0 - pad_h, image): OOB -> zeros
           asm volatile(
@@ -647,56 +638,62 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_co
                   sA + sa * (uint32_t)p.a_stage_bytes),
               "l"(&map_a), "r"(afull0 + 8u * sa), "r"(cb * BLOCK_K), "r"(-p.pad_w), "r"(row0 - p.pad_h), "r"(img + p.in_img0)
               : "memory");
-          for (int t = 0; t < taps; ++t, ++itb) {
-            const uint32_t sb = itb % (uint32_t)p.b_stages, phb = (itb / (uint32_t)p.b_stages) & 1u;
-            mbar_wait(bempty0 + 8u * sb, phb ^ 1u);
+        }
+        __syncwarp();
+        for (int t = 0; t < taps; ++t, ++itb) {
+          const uint32_t sb = itb % (uint32_t)p.b_stages, phb = (itb / (uint32_t)p.b_stages) & 1u;
+          mbar_wait(bempty0 + 8u * sb, phb ^ 1u);
+          if (elect_one()) {
             mbar_arrive_expect_tx(bfull0 + 8u * sb, b_stage_bytes);
             tma_load_2d(sB + sb * b_stage_bytes, &map_b, bfull0 + 8u * sb, (t * p.cblocks + cb) * BLOCK_K, n0);
           }
+          __syncwarp();
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ---------------- MMA issuer ----------------
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
-      uint32_t ita = 0, itb = 0, lt = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-        int img, l0, n0;
-        decode(tile, img, l0, n0);
-        const int loff = l0 - (l0 / p.wp) * p.wp;  // tile's first position inside the loaded rows
-        const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
-        mbar_wait(tempty0 + 8u * a, aph ^ 1u);
+    // ---------------- MMA issuer (warp-uniform loop, one elected lane issues) ----------------
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+    uint32_t ita = 0, itb = 0, lt = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      int img, l0, n0;
+      decode(tile, img, l0, n0);
+      const int loff = l0 - (l0 / p.wp) * p.wp;  // tile's first position inside the loaded rows
+      const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+      mbar_wait(tempty0 + 8u * a, aph ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
+      uint32_t first = 1;
+      for (int cb = 0; cb < p.cblocks; ++cb, ++ita) {
+        const uint32_t sa = ita % (uint32_t)p.a_stages, pha = (ita / (uint32_t)p.a_stages) & 1u;
+        mbar_wait(afull0 + 8u * sa, pha);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
-        uint32_t first = 1;
-        for (int cb = 0; cb < p.cblocks; ++cb, ++ita) {
-          const uint32_t sa = ita % (uint32_t)p.a_stages, pha = (ita / (uint32_t)p.a_stages) & 1u;
-          mbar_wait(afull0 + 8u * sa, pha);
+        const uint32_t a_base = sA + sa * (uint32_t)p.a_stage_bytes;
+        int r = 0, sx = 0;
+        for (int t = 0; t < taps; ++t, ++itb) {
+          const uint32_t sb = itb % (uint32_t)p.b_stages, phb = (itb / (uint32_t)p.b_stages) & 1u;
+          mbar_wait(bfull0 + 8u * sb, phb);
           tc_fence_after();
-          const uint32_t a_base = sA + sa * (uint32_t)p.a_stage_bytes;
-          int r = 0, sx = 0;
-          for (int t = 0; t < taps; ++t, ++itb) {
-            const uint32_t sb = itb % (uint32_t)p.b_stages, phb = (itb / (uint32_t)p.b_stages) & 1u;
-            mbar_wait(bfull0 + 8u * sb, phb);
-            tc_fence_after();
-            const uint32_t a_addr = a_base + (uint32_t)(loff + r * p.wp + sx) * 128u;
-            // the swizzle is a function of the absolute shared-memory address, so a start that is only
-            // 128-byte aligned needs no base_offset (checked on B200: base_offset = (addr >> 7) & 7 is wrong)
-            const uint64_t da = make_sw128_desc(a_addr);
-            const uint64_t db = make_sw128_desc(sB + sb * b_stage_bytes);
+          const uint32_t a_addr = a_base + (uint32_t)(loff + r * p.wp + sx) * 128u;
+          // the swizzle is a function of the absolute shared-memory address, so a start that is only
+          // 128-byte aligned needs no base_offset (checked on B200: base_offset = (addr >> 7) & 7 is wrong)
+          const uint64_t da = make_sw128_desc(a_addr);
+          const uint64_t db = make_sw128_desc(sB + sb * b_stage_bytes);
+          if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / 16; ++k) {
-              umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, first ? 0u : 1u);
-              first = 0;
-            }
+            for (int k = 0; k < BLOCK_K / 16; ++k)
+              umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (first && k == 0) ? 0u : 1u);
             umma_commit(bempty0 + 8u * sb);
-            if (++sx == p.kw) { sx = 0; ++r; }
           }
-          umma_commit(aempty0 + 8u * sa);
+          __syncwarp();
+          first = 0;
+          if (++sx == p.kw) { sx = 0; ++r; }
         }
-        umma_commit(tfull0 + 8u * a);
+        if (elect_one()) umma_commit(aempty0 + 8u * sa);
+        __syncwarp();
       }
+      if (elect_one()) umma_commit(tfull0 + 8u * a);
+      __syncwarp();
     }
   } else {
     // ---------------- epilogue: 4 warps = 128 positions; staged in smem, written with coalesced 16-byte stores ----------------
@@ -890,32 +887,35 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
   if (warp == 0) {
-    if (lane == 0) {
-      // ---------------- TMA producer (both CTAs): own 128 A rows, own half of the weight tile ----------------
-      const int howo = p.ho * p.wo;
-      const uint32_t tx_bytes = 2u * A_STAGE_BYTES + 2u * b_half_bytes;
-      uint32_t it = 0, lt = 0;
-      const uint32_t chunk_bytes = (uint32_t)BLOCK_M * (uint32_t)p.cw * 2u;
-      for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
-        const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
-        const int m0 = mt * 2 * BLOCK_M + (int)rank * BLOCK_M, n0 = nt * p.bn;
-        if (p.has_res) {
-          const uint32_t rb = lt & 1u, rph = (lt >> 1) & 1u;
-          mbar_wait(rempty0 + 8u * rb, rph ^ 1u);
+    // ---------------- TMA producer (both CTAs): own 128 A rows, own half of the weight tile ----------------
+    const int howo = p.ho * p.wo;
+    const uint32_t tx_bytes = 2u * A_STAGE_BYTES + 2u * b_half_bytes;
+    uint32_t it = 0, lt = 0;
+    const uint32_t chunk_bytes = (uint32_t)BLOCK_M * (uint32_t)p.cw * 2u;
+    for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
+      const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
+      const int m0 = mt * 2 * BLOCK_M + (int)rank * BLOCK_M, n0 = nt * p.bn;
+      if (p.has_res) {
+        const uint32_t rb = lt & 1u, rph = (lt >> 1) & 1u;
+        mbar_wait(rempty0 + 8u * rb, rph ^ 1u);
+        if (elect_one()) {
           mbar_arrive_expect_tx(rfull0 + 8u * rb, res_tile_bytes);
           for (int c = 0, ci = 0; c < p.bn; c += p.cw, ++ci)
             tma_load_2d(sR + rb * res_tile_bytes + (uint32_t)ci * chunk_bytes, &map_r, rfull0 + 8u * rb, n0 + c,
                         p.out_row0 + m0);
         }
-        const int img = m0 / howo;
-        const int rem = m0 - img * howo;
-        const int oh = rem / p.wo, ow = rem - oh * p.wo;
-        const int w_base = ow * p.stride - p.pad_w, h_base = oh * p.stride - p.pad_h;
-        int cb = 0, r = 0, sx = 0;
-        for (int j = 0; j < p.num_kb; ++j, ++it) {
-          const uint32_t s = it % (uint32_t)stages;
-          const uint32_t ph = (it / (uint32_t)stages) & 1u;
-          mbar_wait(empty0 + 8u * s, ph ^ 1u);
+        __syncwarp();
+      }
+      const int img = m0 / howo;
+      const int rem = m0 - img * howo;
+      const int oh = rem / p.wo, ow = rem - oh * p.wo;
+      const int w_base = ow * p.stride - p.pad_w, h_base = oh * p.stride - p.pad_h;
+      int cb = 0, r = 0, sx = 0;
+      for (int j = 0; j < p.num_kb; ++j, ++it) {
+        const uint32_t s = it % (uint32_t)stages;
+        const uint32_t ph = (it / (uint32_t)stages) & 1u;
+        mbar_wait(empty0 + 8u * s, ph ^ 1u);
+        if (elect_one()) {
           if (leader) mbar_arrive_expect_tx(full0 + 8u * s, tx_bytes);
           if (p.a_tiled)
             tma2_load_2d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, p.in_row0 + m0);
@@ -923,16 +923,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
             tma2_load_im2col_4d(sA + s * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base,
                                 img + p.in_img0, (uint16_t)sx, (uint16_t)r);
           tma2_load_2d(sB + s * b_half_bytes, &map_b, full0 + 8u * s, j * BLOCK_K, n0 + (int)rank * (p.bn >> 1));
-          if (++cb == p.cpb) {
-            cb = 0;
-            if (++sx == p.kw) { sx = 0; ++r; }
-          }
+        }
+        __syncwarp();
+        if (++cb == p.cpb) {
+          cb = 0;
+          if (++sx == p.kw) { sx = 0; ++r; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && leader) {
-      // ---------------- MMA issuer (leader CTA only) ----------------
+    if (leader) {
+      // ---------------- MMA issuer (leader CTA only; warp-uniform loop, one elected lane issues) ----------------
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)((2 * BLOCK_M) >> 4) << 24);
       uint32_t it = 0, lt = 0;
       for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
@@ -940,6 +941,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
         mbar_wait(tempty0 + 8u * a, aph ^ 1u);  // both CTAs' epilogues have drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
+        int cb = 0;
         for (int j = 0; j < p.num_kb; ++j, ++it) {
           const uint32_t s = it % (uint32_t)stages;
           const uint32_t ph = (it / (uint32_t)stages) & 1u;
@@ -947,12 +949,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
           tc_fence_after();
           const uint64_t da = make_sw128_desc(sA + s * A_STAGE_BYTES);
           const uint64_t db = make_sw128_desc(sB + s * b_half_bytes);
+          const int nk = (cb == p.cpb - 1) ? p.last_kmma : BLOCK_K / 16;
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k)
-            umma2_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((j | k) != 0));
-          umma2_commit_both(empty0 + 8u * s);  // frees the stage in BOTH CTAs
+            for (int k = 0; k < BLOCK_K / 16; ++k)
+              if (k < nk) umma2_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((j | k) != 0));
+            umma2_commit_both(empty0 + 8u * s);  // frees the stage in BOTH CTAs
+          }
+          __syncwarp();
+          if (++cb == p.cpb) cb = 0;
         }
-        umma2_commit_both(tfull0 + 8u * a);
+        if (elect_one()) umma2_commit_both(tfull0 + 8u * a);
+        __syncwarp();
       }
     }
   } else {
@@ -1144,7 +1152,9 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
     const int q_valid = (p.ho - 1) * wp + p.wo;
     const int tiles_img = (q_valid + BLOCK_M - 1) / BLOCK_M;
     const double eff = (double)p.ho * p.wo / ((double)tiles_img * BLOCK_M);
-    const bool want = tune.version == 3 || (tune.version == 0 && eff >= 0.70 && !getenv("DML_NO_V3"));
+    // measured on B200: the layers this kernel targets are bound by tcgen05.mma issue (~190 cycles per
+    // instruction whatever N is), not by operand traffic, so it is opt-in (DML_USE_V3=1) for now
+    const bool want = tune.version == 3 || (tune.version == 0 && eff >= 0.70 && getenv("DML_USE_V3"));
     if (tune.version == 3 && !eligible) return tc_fail("shape is not eligible for the halo kernel");
     if (eligible && want) {
       op.version = 3;
@@ -1200,13 +1210,15 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
     }
   }
   op.version = tune.version == 1 ? 1 : (tune.version == 4 ? 4 : 2);
+  // default: CTA pairs (3-8 % faster on almost every layer) when there are enough 256-row tiles
+  if (tune.version == 0 && !getenv("DML_NO_PAIR") && (long long)n_capacity * p.ho * p.wo >= 2 * BLOCK_M) op.version = 4;
   const bool pair = op.version == 4;  // CTA pairs: 256-row tiles, each CTA stages half of the weight tile
   const long long M_cap = (long long)n_capacity * p.ho * p.wo;
   const long long m_tiles_cap = pair ? (M_cap + 2 * BLOCK_M - 1) / (2 * BLOCK_M) : (M_cap + BLOCK_M - 1) / BLOCK_M;
   op.has_res = op.version != 1 && p.res != nullptr;
   op.bn = op.version == 1 ? pick_bn(p.cout, tune.bn) : pick_bn_v2(p.cout, pair ? 2 * m_tiles_cap : m_tiles_cap, tune.bn);
   // two residual tiles of 128 x bn bf16 live in shared memory: keep them at 64 KiB
-  if (op.has_res && tune.bn == 0 && op.bn > 128) op.bn = pick_bn(p.cout, 0);
+  if (op.has_res && tune.bn == 0 && op.bn > 128 && !pair) op.bn = pick_bn(p.cout, 0);
   if (op.bn == 0) return tc_fail("no N tile for cout = %d (override %d)", p.cout, tune.bn);
   if (p.cin_pad % BLOCK_K) return tc_fail("cin_pad = %d is not a multiple of %d", p.cin_pad, BLOCK_K);
   op.cpb = p.cin_pad / BLOCK_K;
@@ -1336,6 +1348,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.has_res = op.has_res ? 1 : 0;
     k.in_img0 = p.in_img0;
     k.a_tiled = op.a_tiled ? 1 : 0;
+    k.last_kmma = (p.cin - (op.cpb - 1) * BLOCK_K + 15) / 16;
     k.in_row0 = p.in_img0 * p.hi * p.wi;
     k.out_row0 = p.out_row0;
     if ((p.res != nullptr) != op.has_res) return tc_fail("residual pointer does not match the plan");
@@ -1350,32 +1363,11 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.cw = op.cw;
     const int tiles = k.m_tiles * k.n_tiles;
     const int grid = tiles < g_num_sms ? tiles : g_num_sms;
-    static const char* dbg_str = getenv("DML_TC_DEBUG");
-    static const int dbg_val = dbg_str ? atoi(dbg_str) : 0;
-    const bool dbg_env = (dbg_val & 1) != 0;
-    k.dbg = dbg_val;
-    if (dbg_val & 4) k.tmem_cols = 512;
-    if (dbg_env) {
-      static long long zeros[256 * 16] = {};
-      cudaMemcpyToSymbol(g_tc_dbg, zeros, sizeof zeros);
-    }
     if (pair) {
       const int clusters = tiles < g_num_sms / 2 ? tiles : g_num_sms / 2;
       conv_tc2x_kernel<<<2 * clusters, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
     } else
     conv_tc2_kernel<<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
-    if (dbg_env) {
-      static long long host[256 * 16];
-      cudaDeviceSynchronize();
-      cudaMemcpyFromSymbol(host, g_tc_dbg, sizeof host);
-      double acc[8] = {};
-      for (int b = 0; b < grid; ++b) for (int i = 0; i < 8; ++i) acc[i] += (double)host[b * 16 + i];
-      double tiles_cta = acc[7] / grid;
-      fprintf(stderr, "[tc dbg] grid %d bn %d kb %d stages %d tiles/cta %.1f | per tile cycles: prod wait empty %.0f, mma wait tempty %.0f, "
-                      "mma wait full %.0f, epi wait res %.0f, epi wait tfull %.0f, epi wait store-read %.0f, epi work %.0f\n",
-              grid, op.bn, k.num_kb, op.stages, tiles_cta, acc[0] / acc[7], acc[1] / acc[7], acc[2] / acc[7], acc[3] / acc[7],
-              acc[4] / acc[7], acc[5] / acc[7], acc[6] / acc[7]);
-    }
     cudaError_t e2 = cudaGetLastError();
     if (e2 != cudaSuccess) return tc_fail("conv_tc2_kernel launch: %s", cudaGetErrorString(e2));
     return 0;
