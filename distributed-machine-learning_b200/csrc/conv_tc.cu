@@ -1389,11 +1389,30 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
   return 0;
 }
 
+namespace {
+// milliseconds of one launch (after one warm-up), or a huge number if the candidate cannot run
+float time_plan(const TcOpPlan& op, const ConvParams& p, cudaEvent_t e0, cudaEvent_t e1) {
+  if (launch_conv_tc_plan(op, p, nullptr) != 0) return 1e30f;
+  cudaEventRecord(e0, nullptr);
+  for (int i = 0; i < 2; ++i)
+    if (launch_conv_tc_plan(op, p, nullptr) != 0) return 1e30f;
+  cudaEventRecord(e1, nullptr);
+  if (cudaEventSynchronize(e1) != cudaSuccess) return 1e30f;
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  return ms * 0.5f;
+}
+}  // namespace
+
 int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t off_input, size_t off_tc, uint8_t* wts,
             int micro_batch, int max_batch) {
   (void)off_input; (void)off_tc; (void)max_batch;
   plan->ops.assign(net.ops.size(), TcOpPlan());
   plan->micro_batch = micro_batch;
+  const bool autotune = getenv("DML_NO_AUTOTUNE") == nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  if (autotune && (cudaEventCreate(&ev0) != cudaSuccess || cudaEventCreate(&ev1) != cudaSuccess))
+    return tc_fail("autotune: cudaEventCreate failed");
   for (size_t i = 0; i < net.ops.size(); ++i) {
     const Op& op = net.ops[i];
     if (!tc_supported(op)) continue;
@@ -1413,7 +1432,30 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     p.ho = to.h; p.wo = to.w; p.cout = op.cout; p.out_pitch = to.c_pitch;
     p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;
     p.cin_pad = op.cin_pad;
+    p.bias = reinterpret_cast<const float*>(wts + op.bias_off);
+    p.relu = op.relu;
     if (tc_plan_one(&plan->ops[i], p, micro_batch, TcTune()) != 0) return -1;
+    if (!autotune) continue;
+    // Time the candidate kernels / N tiles on the real buffers (contents do not matter) and keep the
+    // fastest.  Every candidate produces bit-identical results (tests/test_gpu_kernels.py).
+    float best = time_plan(plan->ops[i], p, ev0, ev1);
+    for (int version : {4, 2}) {
+      for (int bn : {0, 256, 128, 64}) {
+        if (bn && (op.cout % bn != 0 || bn > op.cout)) continue;
+        TcTune t;
+        t.version = version; t.bn = bn;
+        TcOpPlan cand;
+        if (tc_plan_one(&cand, p, micro_batch, t) != 0) continue;
+        if (cand.version == plan->ops[i].version && cand.bn == plan->ops[i].bn) continue;
+        float ms = time_plan(cand, p, ev0, ev1);
+        if (ms < best * 0.98f) { best = ms; plan->ops[i] = cand; }
+      }
+    }
+  }
+  if (autotune) {
+    cudaEventDestroy(ev0);
+    cudaEventDestroy(ev1);
+    if (cudaDeviceSynchronize() != cudaSuccess) return tc_fail("autotune: %s", cudaGetErrorString(cudaGetLastError()));
   }
   return 0;
 }

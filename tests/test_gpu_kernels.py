@@ -258,3 +258,17 @@ def test_conv_tcgen05_cta_pair(case_id):
     assert (got - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
     if shape[13]:
         assert (out[..., cout:].float() == 7.0).all()
+
+
+def test_conv_tcgen05_variants_are_bit_identical():
+    """Tile shape and kernel variant must not change a single bit (the engine may pick any of them)."""
+    import torch
+    for shape in [(4, 28, 28, 128, 256, 3, 3, 1, 1, 1, True, False, 0, 0), (6, 56, 56, 64, 256, 1, 1, 1, 0, 0, True, True, 0, 0),
+                  (3, 17, 17, 160, 192, 1, 7, 1, 0, 3, True, False, 0, 0)]:
+        rng = np.random.default_rng(2024)
+        case = _conv_case(rng, *shape)
+        big = 128 if shape[4] % 128 == 0 else 96
+        outs = [_run_conv(2, case, 0, 0), _run_conv(2, case, 64, 2), _run_conv(2, case, big, 0), _run_conv(5, case, 0, 0),
+                _run_conv(5, case, 64, 3), _run_conv(1, case, 0, 0)]
+        for o in outs[1:]:
+            assert torch.equal(o, outs[0])
