@@ -8,6 +8,7 @@ runs through libdml_b200.so.  No CPU fallback: without a GPU this raises.
 from __future__ import annotations
 
 import ctypes as C
+import threading
 
 import numpy as np
 
@@ -27,6 +28,7 @@ class Engine:
         if not torch.cuda.is_available():
             raise _lib.DmlError("no CUDA device: the dml_b200 engine has no CPU fallback")
         self.l = _lib.lib()
+        self.lock = threading.Lock()  # one engine is driven by one thread at a time
         self.model_name = model_name
         self.device = device
         self.max_batch = max_batch

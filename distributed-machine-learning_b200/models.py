@@ -85,7 +85,7 @@ def _run(model_name: str, image_files: list, modelObj=None):
     files = list(image_files)
     decoded = list(_pool().map(_decode_one, files))
     good = [i for i, d in enumerate(decoded) if not isinstance(d, str)]
-    with _lock:  # one engine is used by one thread at a time
+    with eng.lock:  # one engine is used by one thread at a time
         idx, prob = eng.predict_images([decoded[i] for i in good])
     results = {}
     pos = {g: k for k, g in enumerate(good)}

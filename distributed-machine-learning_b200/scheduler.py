@@ -157,6 +157,12 @@ class FairShareScheduler:
             return out
         split = self.predicted_split(len(online & set(self.worker_nodes)))
         if split is None:
+            # one worker online: the reference takes min() of an empty list here and raises (worker.py:323);
+            # a single GPU simply alternates, serving the longer queue first
+            model = "InceptionV3" if len(qi) >= len(qr) else "ResNet50"
+            for worker in self._free_workers(online):
+                if self.model_dict[model].queue:
+                    out.append(self._assign(worker, model))
             return out
         want = {"InceptionV3": split[0], "ResNet50": split[1]}
         running = {m: self.get_running_nodes(m) for m in MODELS}

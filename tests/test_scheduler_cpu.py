@@ -87,3 +87,22 @@ def test_failure_requeues_at_the_front_and_c3_quirk():
     assert s.model_dict["ResNet50"].time == pytest.approx(64 + 3.5 + 1 + 0.25 * 63)
     s.set_cost_model("ResNet50", download_time=0, model_load_time=0, first_image_predict_time=0, each_image_predict_time=2e-5)
     assert s.model_dict["ResNet50"].time == pytest.approx(2e-5 * 63)
+
+
+def test_mixed_queues_always_drain(tmp_path):
+    """Whatever the worker count, a mixed job set runs to completion (one worker: alternate models)."""
+    S = pkg("scheduler").FairShareScheduler
+    for nworkers in (1, 2, 3, 8):
+        s = S(W[:nworkers], batch_size=8)
+        s.submit_job("ResNet50", 60, 1, files(100))
+        s.submit_job("InceptionV3", 45, 2, files(100))
+        steps = 0
+        finished = 0
+        while not s.idle():
+            a = s.schedule()
+            running = list(s.workers_tasks_dict)
+            assert running, "nothing running and nothing scheduled: the leader would stall"
+            finished += s.task_done(running[0])
+            steps += 1
+            assert steps < 1000
+        assert finished == 2
