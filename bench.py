@@ -183,6 +183,12 @@ def run_b200(args):
     for i in range(args.warmup):
         eng.infer_ptrs(*ring_dev[i % RING], n)
     barrier()
+    if args.ncu_step:
+        # exactly one step between cudaProfilerStart/Stop: run under `ncu --profile-from-start off`
+        torch.cuda.profiler.start()
+        eng.infer_ptrs(*ring_dev[0], n)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     sampler = ClockSampler(local)
     sampler.start()
     l0 = eng.launch_count()
@@ -248,12 +254,26 @@ def run_b200(args):
             pass
         tf_peak = peaks.get("bf16_tflops_sustained", 1400.0)
         src = "measured (MEASURED_PEAKS.json, sustained)" if peaks else "fallback (B200_PROFILING.md, sustained ~1.4 PF)"
+        # DRAM bytes per launch of the dominant kernel class from the committed ncu capture of this same
+        # step (profiles/*_launches_final_summary.csv; not re-measured here: ncu cannot run inside a timed bench)
+        traffic = None
+        try:
+            import csv as _csv
+            import glob as _glob
+            f = sorted(_glob.glob(os.path.join(ROOT, "profiles", "r*_launches_final_summary.csv")))[-1]
+            rows = [r for r in _csv.DictReader(l for l in open(f) if not l.startswith("#")) if r["kernel"].startswith("conv_tc")]
+            if model == "ResNet50" and rows:
+                traffic = sum(float(r["dram_read_MB"]) + float(r["dram_write_MB"]) for r in rows) * 1e6 / sum(int(r["launches"]) for r in rows)
+        except Exception:
+            traffic = None
         dom = max(per_kind, key=lambda k: per_kind[k]["ms"])
         d = per_kind[dom]
         if dom.startswith("conv"):
             ach = d["flop"] / (d["ms"] * 1e-3) / 1e12
             roof = {"kernel": dom, "bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s",
-                    "frac": ach / tf_peak, "traffic": None, "peak_source": src,
+                    "frac": ach / tf_peak, "traffic": traffic, "traffic_unit": "DRAM bytes per launch (ncu, profiles/)",
+                    "launches_per_step": d["launch_sites"] * ((n + eng_micro(eng, args) - 1) // eng_micro(eng, args)),
+                    "algorithmic_flop_per_launch": d["flop"] / max(1, d["launch_sites"]), "peak_source": src,
                     "share_of_step": d["ms"] / float(ms.sum())}
         else:
             bw_peak = peaks.get("hbm_gbs", 6650.0)
@@ -304,6 +324,7 @@ def main():
     ap.add_argument("--micro-batch", type=int, default=0)
     ap.add_argument("--ops-csv", default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ncu-step", action="store_true", help="bracket one extra step with cudaProfilerStart/Stop")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
