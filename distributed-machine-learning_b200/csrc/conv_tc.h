@@ -43,7 +43,7 @@ struct TcPlan {
 struct TcTune {
   int bn = 0;
   int stages = 0;
-  int version = 0;  // 1 = one tile per CTA, 2 = persistent im2col, 3 = halo kernel, 4 = CTA-pair (cta_group::2) persistent; 0 = choose
+  int version = 0;  // 1 = one tile per CTA, 2 = persistent im2col, 3 = halo kernel, 4 = CTA-pair (cta_group::2) persistent, 5 = weights as A; 0 = choose
 };
 
 bool tc_supported(const Op& op);

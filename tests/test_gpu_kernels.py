@@ -272,3 +272,32 @@ def test_conv_tcgen05_variants_are_bit_identical():
                 _run_conv(5, case, 64, 3), _run_conv(1, case, 0, 0)]
         for o in outs[1:]:
             assert torch.equal(o, outs[0])
+
+
+WEIGHTS_AS_A_CASES = [
+    (2, 56, 56, 64, 64, 3, 3, 1, 1, 1, True, False, 0, 0),
+    (5, 56, 56, 256, 64, 1, 1, 1, 0, 0, True, False, 0, 0),       # tiled pixel operand
+    (9, 28, 28, 128, 128, 3, 3, 1, 1, 1, False, False, 0, 0),
+    (3, 56, 56, 256, 128, 1, 1, 2, 0, 0, True, False, 0, 0),      # stride-2 1x1
+    (2, 35, 35, 48, 64, 5, 5, 1, 2, 2, True, False, 0, 32),       # ragged Cin, concat slice
+    (2, 35, 35, 64, 96, 3, 3, 1, 1, 1, True, False, 0, 160),      # Cout 96
+    (1, 147, 147, 32, 32, 3, 3, 1, 0, 0, True, False, 0, 0),      # Cout 32: three idle epilogue warps
+    (3, 17, 17, 128, 128, 1, 7, 1, 0, 3, True, False, 0, 0),
+    (2, 17, 17, 160, 80, 7, 1, 1, 3, 0, True, False, 576, 0),
+    (1, 5, 5, 64, 32, 1, 1, 1, 0, 0, False, False, 0, 0),
+]
+
+
+@pytest.mark.parametrize("shape", WEIGHTS_AS_A_CASES, ids=lambda s: "x".join(map(str, s[:10])))
+def test_conv_tcgen05_weights_as_a(shape):
+    import torch
+    rng = np.random.default_rng(hash(shape) % 2**32)
+    case = _conv_case(rng, *shape)
+    out = _run_conv(6, case)
+    cout = shape[4]
+    ref = case["ref"]
+    got = out[..., :cout].float()
+    assert (got - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
+    if shape[13]:
+        assert (out[..., cout:].float() == 7.0).all()
+    assert torch.equal(out, _run_conv(2, case))  # same bits as the pixels-as-A kernels
