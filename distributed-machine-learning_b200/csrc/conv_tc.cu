@@ -302,7 +302,8 @@ struct TcV2Params {
 };
 
 constexpr int OUT_BUF_BYTES = 4096;  // 32 rows x 128 B
-constexpr int OUT_STAGING_BYTES = 4 * 2 * OUT_BUF_BYTES;
+constexpr int OUT_STAGING_BYTES = 8 * 2 * OUT_BUF_BYTES;  // 8 epilogue warps x 2 buffers
+constexpr int TC2_THREADS = 320;                       // TMA warp, MMA warp, 8 epilogue warps
 
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
@@ -313,7 +314,7 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t sr
                : "memory");
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_constant__ CUtensorMap map_a,
+__global__ void __launch_bounds__(TC2_THREADS, 1) conv_tc2_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                  const __grid_constant__ CUtensorMap map_b,
                                                                  const __grid_constant__ CUtensorMap map_o,
                                                                  const __grid_constant__ CUtensorMap map_r,
@@ -346,9 +347,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull0 + 8u * i, 1);
-      mbar_init(tempty0 + 8u * i, 4);  // one arrive per epilogue warp
+      mbar_init(tempty0 + 8u * i, 8);  // one arrive per epilogue warp
       mbar_init(rfull0 + 8u * i, 1);
-      mbar_init(rempty0 + 8u * i, 4);
+      mbar_init(rempty0 + 8u * i, 8);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -442,8 +443,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
     }
   } else {
     // ---------------- epilogue warps ----------------
+    // 8 warps: TMEM lane quarter q = warp % 4 (hardware rule), and the two warps of a quarter split the column chunks
     const int q = warp & 3;
-    const uint32_t my_out = sO + (uint32_t)q * 2u * OUT_BUF_BYTES;
+    const int ew = warp - 2, half = ew >> 2;
+    const uint32_t my_out = sO + (uint32_t)ew * 2u * OUT_BUF_BYTES;
     const int cw = p.cw;
     const uint32_t row_bytes = (uint32_t)cw * 2u;
     const uint32_t chunk_bytes = (uint32_t)BLOCK_M * row_bytes;
@@ -458,8 +461,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc2_kernel(const __grid_co
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
       const uint32_t r_row = sR + a * res_tile_bytes + (uint32_t)(q * 32 + lane) * row_bytes;
-      int ci = 0;
-      for (int c0 = 0; c0 < p.bn; c0 += cw, ++nstore, ++ci) {
+      int ci = half;
+      for (int c0 = half * cw; c0 < p.bn; c0 += 2 * cw, ++nstore, ci += 2) {
         const uint32_t sbuf = my_out + (nstore & 1u) * OUT_BUF_BYTES;
         // the TMA store that last read this buffer (two stores ago) must be done reading
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
@@ -833,7 +836,7 @@ __device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & PEER_BIT_MASK) : "memory");
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
     conv_tc2x_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                      const __grid_constant__ CUtensorMap map_o, const __grid_constant__ CUtensorMap map_r,
                      const TcV2Params p) {
@@ -868,9 +871,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull0 + 8u * i, 1);
-      mbar_init(tempty0 + 8u * i, 8);  // leader: 4 epilogue warps of each CTA
+      mbar_init(tempty0 + 8u * i, 16);  // leader: 8 epilogue warps of each CTA
       mbar_init(rfull0 + 8u * i, 1);
-      mbar_init(rempty0 + 8u * i, 4);
+      mbar_init(rempty0 + 8u * i, 8);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -965,8 +968,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
     }
   } else {
     // ---------------- epilogue warps (both CTAs, own 128 rows) ----------------
+    // 8 warps: TMEM lane quarter q = warp % 4 (hardware rule), and the two warps of a quarter split the column chunks
     const int q = warp & 3;
-    const uint32_t my_out = sO + (uint32_t)q * 2u * OUT_BUF_BYTES;
+    const int ew = warp - 2, half = ew >> 2;
+    const uint32_t my_out = sO + (uint32_t)ew * 2u * OUT_BUF_BYTES;
     const int cw = p.cw;
     const uint32_t row_bytes = (uint32_t)cw * 2u;
     const uint32_t chunk_bytes = (uint32_t)BLOCK_M * row_bytes;
@@ -981,8 +986,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
       const uint32_t r_row = sR + a * res_tile_bytes + (uint32_t)(q * 32 + lane) * row_bytes;
-      int ci = 0;
-      for (int c0 = 0; c0 < p.bn; c0 += cw, ++nstore, ++ci) {
+      int ci = half;
+      for (int c0 = half * cw; c0 < p.bn; c0 += 2 * cw, ++nstore, ci += 2) {
         const uint32_t sbuf = my_out + (nstore & 1u) * OUT_BUF_BYTES;
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
         __syncwarp();
@@ -1483,14 +1488,24 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
     op.tmem_cols = 32;
     while (op.tmem_cols < op.bn) op.tmem_cols *= 2;
   } else {
-    const int fixed = 1024 /*alignment slack*/ + OUT_STAGING_BYTES + 256 /*barriers*/ +
-                      (op.has_res ? 2 * BLOCK_M * op.bn * 2 : 0);
-    int target = (SMEM_LIMIT - fixed) / stage_bytes;
+    int fixed = 1024 /*alignment slack*/ + OUT_STAGING_BYTES + 256 /*barriers*/ + (op.has_res ? 2 * BLOCK_M * op.bn * 2 : 0);
+    int sb = stage_bytes;
+    // the two residual tiles may not leave room for two stages at the widest N tile: narrow it (heuristic choice only)
+    while (tune.bn == 0 && (SMEM_LIMIT - fixed) / sb < 2 && op.bn > 64) {
+      int nb = 0;
+      for (int c = op.bn - 16; c >= 16; c -= 16)
+        if (p.cout % c == 0) { nb = c; break; }
+      if (!nb) break;
+      op.bn = nb;
+      fixed = 1024 + OUT_STAGING_BYTES + 256 + (op.has_res ? 2 * BLOCK_M * op.bn * 2 : 0);
+      sb = A_STAGE_BYTES + (pair ? op.bn * 64 : op.bn * 128);
+    }
+    int target = (SMEM_LIMIT - fixed) / sb;
     if (target > 8) target = 8;
     if (tune.stages > 0 && tune.stages < target) target = tune.stages;
     if (target < 2) return tc_fail("not enough shared memory for 2 stages at bn = %d", op.bn);
     op.stages = target;
-    op.smem = (size_t)op.stages * stage_bytes + fixed;
+    op.smem = (size_t)op.stages * sb + fixed;
     op.acc_stride = 32;
     while (op.acc_stride < op.bn) op.acc_stride *= 2;
     op.tmem_cols = 2 * op.acc_stride;
@@ -1638,9 +1653,9 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     const int grid = tiles < g_num_sms ? tiles : g_num_sms;
     if (pair) {
       const int clusters = tiles < g_num_sms / 2 ? tiles : g_num_sms / 2;
-      conv_tc2x_kernel<<<2 * clusters, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
+      conv_tc2x_kernel<<<2 * clusters, TC2_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
     } else
-    conv_tc2_kernel<<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
+    conv_tc2_kernel<<<grid, TC2_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
     cudaError_t e2 = cudaGetLastError();
     if (e2 != cudaSuccess) return tc_fail("conv_tc2_kernel launch: %s", cudaGetErrorString(e2));
     return 0;
