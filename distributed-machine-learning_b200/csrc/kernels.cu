@@ -233,37 +233,90 @@ __global__ void __launch_bounds__(256) pool_kernel(PoolParams p) {
   *reinterpret_cast<uint4*>(out) = *reinterpret_cast<uint4*>(o);
 }
 
+// K4 fast path (bf16, 3x3): the nine 16-byte loads are issued back to back and reduced with packed
+// bf16x2 max (exact: max of bf16 values is a bf16 value); an out-of-bounds tap contributes 0.
+__global__ void __launch_bounds__(256) maxpool3_bf16_kernel(PoolParams p) {
+  const int cg = p.c >> 3;
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)p.n * p.ho * p.wo * cg) return;
+  const int g = (int)(idx % cg);
+  int64_t pix = idx / cg;
+  const int wo = (int)(pix % p.wo);
+  int64_t t = pix / p.wo;
+  const int ho = (int)(t % p.ho);
+  const int n = (int)(t / p.ho);
+  const __nv_bfloat16* in = reinterpret_cast<const __nv_bfloat16*>(p.in) + (int64_t)n * p.hi * p.wi * p.in_pitch + g * 8;
+  const int h0 = ho * p.stride - p.pad, w0 = wo * p.stride - p.pad;
+  uint4 raw[9];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+      const int hi = h0 + r, wi = w0 + s;
+      raw[r * 3 + s] = make_uint4(0, 0, 0, 0);  // bf16 zeros = what ZeroPadding2D contributes
+      if (hi >= 0 && hi < p.hi && wi >= 0 && wi < p.wi)
+        raw[r * 3 + s] = *reinterpret_cast<const uint4*>(in + ((int64_t)hi * p.wi + wi) * p.in_pitch);
+    }
+  // pad == 0: every tap is in bounds, so starting from tap 0 is exact; pad > 0: zeros take part like any tap
+  __nv_bfloat162 m[4];
+  {
+    const __nv_bfloat162* v = reinterpret_cast<const __nv_bfloat162*>(&raw[0]);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) m[i] = v[i];
+  }
+#pragma unroll
+  for (int k = 1; k < 9; ++k) {
+    const __nv_bfloat162* v = reinterpret_cast<const __nv_bfloat162*>(&raw[k]);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) m[i] = __hmax2(m[i], v[i]);
+  }
+  __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out) + (((int64_t)n * p.ho + ho) * p.wo + wo) * p.out_pitch + g * 8;
+  *reinterpret_cast<uint4*>(out) = *reinterpret_cast<const uint4*>(m);
+}
+
 // K5 fast path (3x3, stride 1, pad 1): one thread per (image, output column, channel
 // group) walks down the rows keeping the last three horizontal 3-tap sums, so each
 // output costs 3 loads instead of 9; divisor = valid rows x valid columns.
+constexpr int AVG_ROWS = 6;  // output rows per thread: more threads in flight than one thread per column
 template <typename T>
 __global__ void __launch_bounds__(256) avgpool3_kernel(PoolParams p) {
   constexpr int V = Vec16<T>::N;
   const int cg = p.c / V;
+  const int segs = (p.hi + AVG_ROWS - 1) / AVG_ROWS;
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (int64_t)p.n * p.wi * cg) return;
+  if (idx >= (int64_t)p.n * segs * p.wi * cg) return;
   const int g = (int)(idx % cg);
   const int wo = (int)((idx / cg) % p.wi);
-  const int n = (int)(idx / ((int64_t)cg * p.wi));
+  const int seg = (int)((idx / ((int64_t)cg * p.wi)) % segs);
+  const int n = (int)(idx / ((int64_t)cg * p.wi * segs));
   const T* in = reinterpret_cast<const T*>(p.in) + (int64_t)n * p.hi * p.wi * p.in_pitch + g * V;
   T* out = reinterpret_cast<T*>(p.out) + (int64_t)n * p.hi * p.wi * p.out_pitch + g * V;
   const int w0 = wo > 0 ? wo - 1 : 0, w1 = wo < p.wi - 1 ? wo + 1 : p.wi - 1;
   const float ncols = (float)(w1 - w0 + 1);
+  const int r_begin = seg * AVG_ROWS, r_end = r_begin + AVG_ROWS < p.hi ? r_begin + AVG_ROWS : p.hi;
   float h0[V], h1[V], h2[V];  // horizontal sums of rows r-1, r, r+1
 #pragma unroll
   for (int i = 0; i < V; ++i) h0[i] = h1[i] = h2[i] = 0.f;
   auto hsum = [&](int r, float (&h)[V]) {
+    uint4 raw[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int wi = w0 + j;
+      raw[j] = make_uint4(0, 0, 0, 0);
+      if (wi <= w1) raw[j] = *reinterpret_cast<const uint4*>(in + ((int64_t)r * p.wi + wi) * p.in_pitch);
+    }
 #pragma unroll
     for (int i = 0; i < V; ++i) h[i] = 0.f;
-    for (int wi = w0; wi <= w1; ++wi) {
-      uint4 raw = *reinterpret_cast<const uint4*>(in + ((int64_t)r * p.wi + wi) * p.in_pitch);
-      const T* v = reinterpret_cast<const T*>(&raw);
 #pragma unroll
-      for (int i = 0; i < V; ++i) h[i] += to_f(v[i]);
+    for (int j = 0; j < 3; ++j) {
+      const T* v = reinterpret_cast<const T*>(&raw[j]);
+#pragma unroll
+      for (int i = 0; i < V; ++i) h[i] += to_f(v[i]);  // same left-to-right order as before: w0, w0+1, w0+2
     }
   };
-  hsum(0, h1);
-  for (int r = 0; r < p.hi; ++r) {
+  if (r_begin > 0) hsum(r_begin - 1, h0);
+  hsum(r_begin, h1);
+  for (int r = r_begin; r < r_end; ++r) {
     const bool has_next = r + 1 < p.hi;
     if (has_next) hsum(r + 1, h2);
     const float nrows = (float)((r > 0) + 1 + has_next);
@@ -449,11 +502,18 @@ static void launch_pool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
   if (fp32_act) pool_kernel<float, AVG><<<blocks, 256, 0, s>>>(p);
   else pool_kernel<__nv_bfloat16, AVG><<<blocks, 256, 0, s>>>(p);
 }
-void launch_maxpool(const PoolParams& p, bool fp32_act, cudaStream_t s) { launch_pool<false>(p, fp32_act, s); }
+void launch_maxpool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
+  if (!fp32_act && p.k == 3) {
+    int64_t total = (int64_t)p.n * p.ho * p.wo * (p.c / 8);
+    maxpool3_bf16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(p);
+    return;
+  }
+  launch_pool<false>(p, fp32_act, s);
+}
 void launch_avgpool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
   if (p.k == 3 && p.stride == 1 && p.pad == 1 && p.ho == p.hi && p.wo == p.wi) {
     int V = fp32_act ? 4 : 8;
-    int64_t total = (int64_t)p.n * p.wi * (p.c / V);
+    int64_t total = (int64_t)p.n * ((p.hi + AVG_ROWS - 1) / AVG_ROWS) * p.wi * (p.c / V);
     unsigned blocks = (unsigned)((total + 255) / 256);
     if (fp32_act) avgpool3_kernel<float><<<blocks, 256, 0, s>>>(p);
     else avgpool3_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(p);
