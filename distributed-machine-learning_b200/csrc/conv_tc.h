@@ -56,5 +56,8 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
 int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s);
 int launch_conv_tc(const TcPlan& plan, int op_index, const ConvParams& p, int img0, cudaStream_t s, int* nlaunch);
 const char* tc_last_error();
+// Tiled bf16 tensor map (rank <= 5) for kernels outside conv_tc.cu; swizzle_bytes in {0, 32, 64, 128}.
+int tc_make_tiled_map(CUtensorMap* out, void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box, int swizzle_bytes);
 
 }  // namespace dml
