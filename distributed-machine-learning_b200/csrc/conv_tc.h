@@ -17,6 +17,7 @@ struct TcOpPlan {
   alignas(64) CUtensorMap map_b;  // tiled map over packed weights [cout][taps*cin_pad]
   int bn = 0;        // N tile (output channels per CTA)
   int stages = 0;
+  int group = 1;     // k-blocks per pipeline stage (v2 / v4)
   int tmem_cols = 0;
   int cpb = 0;       // 64-channel blocks per tap
   size_t smem = 0;
@@ -32,6 +33,8 @@ struct TcOpPlan {
   // v3 (halo kernel)
   int wp = 0, rows_box = 0, tiles_per_img = 0, q_valid = 0, a_stage_bytes = 0, a_stages = 0, b_stages = 0;
   int desc_mode = 0;
+  // v6 (halo kernel, resident filter)
+  int a_cb_bytes = 0, row_bytes = 0;
 };
 
 struct TcPlan {
@@ -43,7 +46,8 @@ struct TcPlan {
 struct TcTune {
   int bn = 0;
   int stages = 0;
-  int version = 0;  // 1 = one tile per CTA, 2 = persistent im2col, 3 = halo kernel, 4 = CTA-pair (cta_group::2) persistent, 5 = weights as A; 0 = choose
+  int group = 0;    // k-blocks per pipeline stage for v2 / v4 (0 = heuristic)
+  int version = 0;  // 1 = one tile per CTA, 2 = persistent im2col, 3 = halo kernel, 4 = CTA-pair (cta_group::2) persistent, 5 = weights as A, 6 = halo kernel with the filter resident in shared memory; 0 = choose
 };
 
 bool tc_supported(const Op& op);

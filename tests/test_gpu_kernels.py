@@ -260,6 +260,37 @@ def test_conv_tcgen05_cta_pair(case_id):
         assert (out[..., cout:].float() == 7.0).all()
 
 
+RESIDENT_HALO_CASES = [
+    # n, hi, wi, cin, cout, kh, kw, stride, pad_h, pad_w, relu, res, in_extra, out_extra
+    (2, 56, 56, 64, 64, 3, 3, 1, 1, 1, True, False, 0, 0),         # ResNet50 conv2 3x3
+    (300, 14, 14, 64, 64, 3, 3, 1, 1, 1, False, False, 0, 0),      # more tiles than SMs: ring and accumulators wrap
+    (2, 149, 149, 32, 32, 3, 3, 1, 0, 0, True, False, 0, 0),       # InceptionV3 conv2d_1: 64-byte rows, valid conv
+    (1, 147, 147, 32, 64, 3, 3, 1, 1, 1, True, False, 0, 0),       # conv2d_2: 64-byte rows, same padding
+    (3, 35, 35, 64, 96, 3, 3, 1, 1, 1, True, False, 0, 160),       # Cout 96 into a concat slice
+    (2, 35, 35, 48, 64, 3, 3, 1, 1, 1, True, False, 16, 0),        # ragged Cin, input is a channel slice
+    (2, 20, 20, 16, 32, 5, 5, 1, 2, 2, True, False, 0, 0),         # 5x5, one K step
+    (2, 17, 17, 24, 48, 1, 7, 1, 0, 3, False, False, 8, 16),       # 1x7, ragged 64-byte rows
+    (2, 17, 17, 96, 48, 7, 1, 1, 3, 0, True, False, 0, 0),         # 7x1, two channel blocks, Cout 48
+    (2, 30, 30, 128, 32, 3, 3, 1, 1, 1, True, False, 0, 0),        # 3x3 with two channel blocks (compile-time path)
+]
+
+
+@pytest.mark.parametrize("shape", RESIDENT_HALO_CASES, ids=lambda s: "x".join(map(str, s[:10])))
+def test_conv_tcgen05_resident_filter_halo(shape):
+    """impl 7: halo kernel with the whole filter resident in shared memory (both row widths)."""
+    import torch
+    rng = np.random.default_rng(hash(shape) % 2**32)
+    case = _conv_case(rng, *shape)
+    out = _run_conv(7, case)
+    cout = shape[4]
+    ref = case["ref"]
+    got = out[..., :cout].float()
+    assert (got - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
+    if shape[13]:
+        assert (out[..., cout:].float() == 7.0).all()
+    assert torch.equal(out, _run_conv(2, case))   # same bits as the im2col kernel
+
+
 def test_conv_tcgen05_variants_are_bit_identical():
     """Tile shape and kernel variant must not change a single bit (the engine may pick any of them)."""
     import torch
@@ -268,8 +299,11 @@ def test_conv_tcgen05_variants_are_bit_identical():
         rng = np.random.default_rng(2024)
         case = _conv_case(rng, *shape)
         big = 128 if shape[4] % 128 == 0 else 96
+        g = lambda k, stages=0: (k << 8) | stages   # k-blocks per pipeline stage ride in bits 8..15 of `stages`
         outs = [_run_conv(2, case, 0, 0), _run_conv(2, case, 64, 2), _run_conv(2, case, big, 0), _run_conv(5, case, 0, 0),
-                _run_conv(5, case, 64, 3), _run_conv(1, case, 0, 0)]
+                _run_conv(5, case, 64, 3), _run_conv(1, case, 0, 0), _run_conv(2, case, 64, g(1)), _run_conv(2, case, 64, g(4)),
+                _run_conv(2, case, 32, g(5, 2)), _run_conv(5, case, 64, g(1)), _run_conv(5, case, 64, g(3)),
+                _run_conv(5, case, big, g(2, 2)), _run_conv(5, case, 32, g(7))]
         for o in outs[1:]:
             assert torch.equal(o, outs[0])
 
