@@ -73,6 +73,7 @@ _SIGS = {
     "dml_tensor_info": [_vp, _i, C.c_char_p, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_vp),
                         C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)],
     "dml_input_tensor": [_vp, C.POINTER(_vp), C.POINTER(_i)],
+    "dml_input_layout": [_vp, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)],
     "dml_logits": [_vp, C.POINTER(_vp)],
     "dml_launch_count": [_vp, C.POINTER(_i64)],
     "dml_num_ops": [_vp, C.POINTER(_i)],

@@ -68,6 +68,14 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 // Bounded wait: a protocol bug traps (kernel error) instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(done)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  if (done) return;  // already complete: no clock read on the fast path
   long long t0 = clock64();
   while (true) {
     asm volatile(
@@ -866,8 +874,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_co
 // (tools/mma_bench.cu: +106 cycles per try_wait at N = 64).  Here nothing is waited for inside a tile:
 // every tap's weight tile is loaded ONCE per CTA, the input halo of a tile (all channel blocks) arrives
 // behind one barrier, and the MMA warp issues taps x blocks x K-steps instructions back to back.
-// Channel blocks are 64 wide (128-byte rows, SWIZZLE_128B) or, for Cin <= 32, 32 wide (64-byte rows,
-// SWIZZLE_64B), which halves the staged bytes of those layers.
+// Channel blocks are 64 wide (128-byte rows, SWIZZLE_128B), for Cin <= 32 32 wide (64-byte rows, SWIZZLE_64B)
+// and for Cin <= 16 16 wide (32-byte rows, SWIZZLE_32B: one K = 16 step per tap), which shrinks the staged
+// bytes of those layers accordingly.  The padded raster is Wp = Wo + kw - 1 wide and starts pad_w columns /
+// pad_h rows before the image (the pads on the far side may differ: the space-to-depth stems use that).
+constexpr int TC6_THREADS = 320;  // producer warp, MMA warp, 8 epilogue warps
+
+// (image, tile inside the image) of a persistent CTA's tiles without a division per tile
+struct TileWalk {
+  int img, mt, tpi, dimg, dmt;
+  __device__ TileWalk(int tiles_per_img, int first, int stride) : tpi(tiles_per_img) {
+    img = first / tpi; mt = first - img * tpi;
+    dimg = stride / tpi; dmt = stride - dimg * tpi;
+  }
+  __device__ void next() {
+    img += dimg; mt += dmt;
+    if (mt >= tpi) { mt -= tpi; ++img; }
+  }
+};
+
 struct TcV6Params {
   const float* bias;
   __nv_bfloat16* out;
@@ -881,11 +906,18 @@ struct TcV6Params {
   int last_kmma;   // K = 16 steps that carry real channels in the last channel block
   int cin_pad;     // weight row layout: [tap][cin_pad]
   int prof;
+  int wide_store;  // output rows are 32-byte aligned: 256-bit stores
+  int n_acc;       // TMEM accumulators (2 or 4)
+  float inv_wp;    // 1 / wp
 };
 
+// q / wp for 0 <= q < 2^16 and wp <= 256 without an integer division: (q + 0.5) / wp is at least 0.5 / 256 away from
+// every integer, far more than the float rounding error of the product
+__device__ __forceinline__ int div_wp(int q, float inv_wp) { return __float2int_rz(((float)q + 0.5f) * inv_wp); }
+
 __device__ __forceinline__ uint64_t make_sw_desc(uint32_t smem_addr, uint32_t row_bytes) {
-  // rows `row_bytes` apart, 8-row groups 8 * row_bytes apart (SBO); layout 2 = SWIZZLE_128B, 4 = SWIZZLE_64B
-  const uint64_t layout = row_bytes == 128u ? 2ull : 4ull;
+  // rows `row_bytes` apart, 8-row groups 8 * row_bytes apart (SBO); layout 2 = SWIZZLE_128B, 4 = SWIZZLE_64B, 6 = SWIZZLE_32B
+  const uint64_t layout = row_bytes == 128u ? 2ull : (row_bytes == 64u ? 4ull : 6ull);
   return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)1 << 16) | ((uint64_t)((8u * row_bytes) >> 4) << 32) |
          ((uint64_t)1 << 46) | (layout << 61);
 }
@@ -895,7 +927,7 @@ __device__ __forceinline__ uint64_t make_sw_desc(uint32_t smem_addr, uint32_t ro
 // warp runs ~50 dependent (uniform-datapath) instructions per k-block in the generic loop, which costs more
 // than the four short MMAs it issues (DML_TC_PROF counters).
 template <int KH, int KW, int CBLOCKS, int ROW_BYTES>
-__global__ void __launch_bounds__(TC_THREADS, 1) conv_tc6_kernel(const __grid_constant__ CUtensorMap map_a,
+__global__ void __launch_bounds__(TC6_THREADS, 1) conv_tc6_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                  const __grid_constant__ CUtensorMap map_b,
                                                                  const TcV6Params p) {
   extern __shared__ uint8_t smem_raw[];
@@ -909,8 +941,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc6_kernel(const __grid_co
   const uint32_t bars = (sO + (uint32_t)p.bn * 4u + 15u) & ~15u;
   const uint32_t afull0 = bars, aempty0 = afull0 + 8u * p.a_stages;
   const uint32_t bfull = aempty0 + 8u * p.a_stages;
-  const uint32_t tfull0 = bfull + 8u, tempty0 = tfull0 + 16u;
-  const uint32_t tmem_slot = tempty0 + 16u;
+  const uint32_t tfull0 = bfull + 8u, tempty0 = tfull0 + 32u;  // up to 4 accumulators
+  const uint32_t tmem_slot = tempty0 + 32u;
+  const uint32_t n_acc = (uint32_t)p.n_acc;  // 2 or 4
+  const uint32_t acc_shift = n_acc == 4u ? 2u : 1u;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.n_img * p.tiles_per_img;
@@ -922,7 +956,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc6_kernel(const __grid_co
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
     for (int i = 0; i < p.a_stages; ++i) { mbar_init(afull0 + 8u * i, 1); mbar_init(aempty0 + 8u * i, 1); }
     mbar_init(bfull, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(tfull0 + 8u * i, 1); mbar_init(tempty0 + 8u * i, 4); }
+    for (int i = 0; i < 4; ++i) { mbar_init(tfull0 + 8u * i, 1); mbar_init(tempty0 + 8u * i, 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -948,11 +982,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc6_kernel(const __grid_co
     __syncwarp();
     uint32_t ita = 0;
     const uint32_t box_bytes = (uint32_t)p.rows_box * (uint32_t)p.wp * row_bytes;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ita) {
-      const int img = tile / p.tiles_per_img;
-      const int l0 = (tile - img * p.tiles_per_img) * BLOCK_M;
-      const int row0 = l0 / p.wp;  // first padded row the tile touches
-      const uint32_t sa = ita % (uint32_t)p.a_stages, pha = (ita / (uint32_t)p.a_stages) & 1u;
+    TileWalk tw(p.tiles_per_img, (int)blockIdx.x, (int)gridDim.x);
+    uint32_t sa = 0, pha = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ita, tw.next(), pha ^= (++sa == (uint32_t)p.a_stages), sa = sa == (uint32_t)p.a_stages ? 0u : sa) {
+      const int img = tw.img;
+      const int l0 = tw.mt * BLOCK_M;
+      const int row0 = div_wp(l0, p.inv_wp);  // first padded row the tile touches
       const long long w0 = p.prof ? clock64() : 0;
       mbar_wait(aempty0 + 8u * sa, pha ^ 1u);
       if (p.prof) prof[0] += clock64() - w0;
@@ -974,12 +1009,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc6_kernel(const __grid_co
     const int ksteps = p.row_bytes >> 5;
     mbar_wait(bfull, 0);
     uint32_t ita = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ita) {
-      const int img = tile / p.tiles_per_img;
-      const int l0 = (tile - img * p.tiles_per_img) * BLOCK_M;
-      const int loff = l0 - (l0 / p.wp) * p.wp;  // tile's first position inside the loaded rows
-      const uint32_t a = ita & 1u, aph = (ita >> 1) & 1u;
-      const uint32_t sa = ita % (uint32_t)p.a_stages, pha = (ita / (uint32_t)p.a_stages) & 1u;
+    TileWalk tw(p.tiles_per_img, (int)blockIdx.x, (int)gridDim.x);
+    uint32_t sa = 0, pha = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ita, tw.next(), pha ^= (++sa == (uint32_t)p.a_stages), sa = sa == (uint32_t)p.a_stages ? 0u : sa) {
+      const int l0 = tw.mt * BLOCK_M;
+      const int loff = l0 - div_wp(l0, p.inv_wp) * p.wp;  // tile's first position inside the loaded rows
+      const uint32_t a = ita & (n_acc - 1u), aph = (ita >> acc_shift) & 1u;
       const long long w1 = p.prof ? clock64() : 0;
       mbar_wait(tempty0 + 8u * a, aph ^ 1u);
       const long long w2 = p.prof ? clock64() : 0;
@@ -1045,21 +1080,27 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc6_kernel(const __grid_co
     // cycles per tile: one warp per scheduler cannot hide that instruction stream) and against one 1-D bulk copy
     // per thread (~22 cycles of TMA issue per copy): the strided 16-byte stores cost ~900 cycles per tile and L2
     // merges them into full lines before they reach HBM.
+    // 8 warps in two groups of 4 (TMEM lane quarter q = warp % 4, hardware rule).  Group g drains the tiles with
+    // lt % 2 == g, so two tiles are in the epilogue at once: one tile's chain (TMEM load -> bias/ReLU/pack -> store)
+    // is latency-bound, and with up to four accumulators the MMA warp keeps issuing meanwhile.
     const int q = warp & 3;
-    const int et = q * 32 + lane;  // epilogue thread id = tile row
+    const int grp = (warp - 2) >> 2;
+    const int et = q * 32 + lane;  // tile row
     const uint32_t sbias = sO;
-    for (int c = et; c < p.bn; c += 128) {
+    for (int c = (int)threadIdx.x - 64; c < p.bn; c += 256) {
       const float bv = __ldg(p.bias + c);
       asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias + (uint32_t)c * 4u), "f"(bv) : "memory");
     }
-    named_bar_sync(1, 128);
-    uint32_t lt = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-      const int img = tile / p.tiles_per_img;
-      const int l0 = (tile - img * p.tiles_per_img) * BLOCK_M;
-      const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+    named_bar_sync(1, 256);
+    const int g_begin = 0, g_end = p.bn;
+    uint32_t lt = (uint32_t)grp;
+    TileWalk tw(p.tiles_per_img, (int)blockIdx.x + grp * (int)gridDim.x, 2 * (int)gridDim.x);
+    for (int tile = blockIdx.x + grp * gridDim.x; tile < total_tiles; tile += 2 * gridDim.x, lt += 2, tw.next()) {
+      const int img = tw.img;
+      const int l0 = tw.mt * BLOCK_M;
+      const uint32_t a = lt & (n_acc - 1u), aph = (lt >> acc_shift) & 1u;
       const int pos = l0 + et;
-      const int hp = pos / p.wp, wq = pos - hp * p.wp;
+      const int hp = div_wp(pos, p.inv_wp), wq = pos - hp * p.wp;
       const bool valid = hp < p.ho && wq < p.wo;
       const long long off = ((long long)((img + p.out_img0) * p.ho + hp) * p.wo + wq) * p.out_pitch;
       const long long w4 = p.prof ? clock64() : 0;
@@ -1067,9 +1108,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc6_kernel(const __grid_co
       if (p.prof) prof[3] += clock64() - w4;
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
-      for (int g = 0; g < p.bn; g += 32) {
+      for (int g = g_begin; g < g_end; g += 32) {
         uint32_t v[2][16];
-        const bool two = g + 16 < p.bn;
+        const bool two = g + 16 < g_end;
         tmem_ld16_nowait(t_row + (uint32_t)g, v[0]);
         if (two) tmem_ld16_nowait(t_row + (uint32_t)(g + 16), v[1]);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
@@ -1091,10 +1132,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc6_kernel(const __grid_co
             pk[2 * i] = *reinterpret_cast<uint32_t*>(&lo);
             pk[2 * i + 1] = *reinterpret_cast<uint32_t*>(&hi);
           }
-          if (valid) {
-            uint4* dst = reinterpret_cast<uint4*>(p.out + off + gg);
-            dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-            dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          if (valid && p.wide_store != 2) {
+            if (p.wide_store) {  // one 32-byte store: a whole sector per thread
+              asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p.out + off + gg), "r"(pk[0]), "r"(pk[1]),
+                           "r"(pk[2]), "r"(pk[3]), "r"(pk[4]), "r"(pk[5]), "r"(pk[6]), "r"(pk[7])
+                           : "memory");
+            } else {
+              uint4* dst = reinterpret_cast<uint4*>(p.out + off + gg);
+              dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            }
           }
         }
       }
@@ -1666,6 +1713,8 @@ int tc_init() {
   e = cudaFuncSetAttribute(conv_tc6_kernel<3, 3, 1, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<3, 3, 1, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<3, 3, 2, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<4, 4, 1, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<2, 2, 1, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<0, 0, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc6_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
@@ -1763,8 +1812,8 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
   }
   // ---- v6: halo kernel with the whole filter resident (few-channel stride-1 multi-tap layers) ----
   if (tune.version == 6 || tune.version == 0) {
-    const int wp = p.wi + 2 * p.pad_w;
-    const int row_bytes = p.cin <= 32 ? 64 : 128;
+    const int wp = p.wo + p.kw - 1;
+    const int row_bytes = p.cin <= 16 ? 32 : (p.cin <= 32 ? 64 : 128);
     const int kb = row_bytes / 2;
     const int cblocks = (p.cin + kb - 1) / kb;
     const int taps = p.kh * p.kw;
@@ -1786,7 +1835,7 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
       v6.bn = p.cout;
       v6.acc_stride = 32;
       while (v6.acc_stride < v6.bn) v6.acc_stride *= 2;
-      v6.tmem_cols = 2 * v6.acc_stride;
+      v6.tmem_cols = v6.acc_stride <= 128 ? 4 * v6.acc_stride : 2 * v6.acc_stride;  // four accumulators when they fit
       v6.cw = v6.bn % 64 == 0 ? 64 : (v6.bn % 32 == 0 ? 32 : 16);
       const int b_bytes = (taps * cblocks * v6.bn * row_bytes + 1023) / 1024 * 1024;
       const int fixed = 1024 + b_bytes + v6.bn * 4 + 16 + 512;
@@ -1794,12 +1843,12 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
       if (v6.a_stages > 4) v6.a_stages = 4;
       if (tune.stages > 0 && tune.stages < v6.a_stages) v6.a_stages = tune.stages;
       const double eff = (double)p.ho * p.wo / ((double)v6.tiles_per_img * BLOCK_M);
-      const bool fits = v6.rows_box <= 256 && v6.a_stages >= 2;
+      const bool fits = v6.rows_box <= 256 && v6.a_stages >= 2 && (long long)v6.tiles_per_img * BLOCK_M < 65536;
       if (tune.version == 6 && !fits) return tc_fail("resident-filter halo kernel does not fit in shared memory for this shape");
       if (fits && (tune.version == 6 || (eff >= 0.70 && !getenv("DML_NO_V6")))) {
         v6.smem = (size_t)fixed + (size_t)v6.a_stages * v6.a_stage_bytes;
         v6.m_capacity = n_capacity;
-        const CUtensorMapSwizzle sw = row_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+        const CUtensorMapSwizzle sw = row_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (row_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
         cuuint64_t gdim[4] = {(cuuint64_t)p.cin, (cuuint64_t)p.wi, (cuuint64_t)p.hi, (cuuint64_t)n_capacity};
         cuuint64_t gstr[3] = {(cuuint64_t)p.in_pitch * 2, (cuuint64_t)p.wi * p.in_pitch * 2, (cuuint64_t)p.hi * p.wi * p.in_pitch * 2};
         cuuint32_t box[4] = {(cuuint32_t)kb, (cuuint32_t)wp, (cuuint32_t)v6.rows_box, 1};
@@ -2057,16 +2106,24 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.cin_pad = p.cin_pad;
     const int tiles = p.n * op.tiles_per_img;
     const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+    k.n_acc = op.tmem_cols / op.acc_stride;
+    k.inv_wp = 1.0f / (float)op.wp;
+    k.wide_store = (p.out_pitch % 16 == 0 && reinterpret_cast<uintptr_t>(p.out) % 32 == 0 && !getenv("DML_NO_WIDE_STORE")) ? 1 : 0;
+    if (getenv("DML_V6_NOSTORE")) k.wide_store = 2;  // experiment: skip the epilogue's global stores
     static const bool prof6 = getenv("DML_TC_PROF") != nullptr;
     k.prof = prof6 ? 1 : 0;
     if (p.kh == 3 && p.kw == 3 && op.cpb == 1 && op.row_bytes == 128)
-      conv_tc6_kernel<3, 3, 1, 128><<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+      conv_tc6_kernel<3, 3, 1, 128><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
     else if (p.kh == 3 && p.kw == 3 && op.cpb == 1 && op.row_bytes == 64)
-      conv_tc6_kernel<3, 3, 1, 64><<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+      conv_tc6_kernel<3, 3, 1, 64><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
     else if (p.kh == 3 && p.kw == 3 && op.cpb == 2 && op.row_bytes == 128)
-      conv_tc6_kernel<3, 3, 2, 128><<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+      conv_tc6_kernel<3, 3, 2, 128><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+    else if (p.kh == 4 && p.kw == 4 && op.cpb == 1 && op.row_bytes == 32)
+      conv_tc6_kernel<4, 4, 1, 32><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+    else if (p.kh == 2 && p.kw == 2 && op.cpb == 1 && op.row_bytes == 32)
+      conv_tc6_kernel<2, 2, 1, 32><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
     else
-      conv_tc6_kernel<0, 0, 0, 0><<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+      conv_tc6_kernel<0, 0, 0, 0><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
     if (prof6) {
       cudaStreamSynchronize(s);
       static long long h[160 * 8];

@@ -82,6 +82,9 @@ struct dml_engine {
   size_t off_lut = 0, off_input = 0, off_arena = 0, off_pooled = 0, off_logits = 0, off_tc = 0, ws_need = 0;
   int64_t launches = 0;
   dml::TcPlan tc;  // tensor maps etc. for the tcgen05 path
+  bool s2d = false;          // K1 writes the space-to-depth input and the stem runs as a stride-1 halo conv (Net::S2d)
+  size_t input_img_bytes = 0;
+  dml::TcOpPlan stem_plan;
   // profiling (dml_profile_forward): one event pair per op launch
   bool profiling = false;
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof;
@@ -100,10 +103,7 @@ struct dml_engine {
 
   void* tensor_ptr(int t, int img0) const {
     const dml::Tensor& tt = net.tensors[t];
-    if (tt.buf == -1) {
-      size_t per = (size_t)net.input_size * net.input_size * 3 * act_bytes;
-      return ws + off_input + per * img0;
-    }
+    if (tt.buf == -1) return ws + off_input + input_img_bytes * img0;
     if (tt.buf == -2) return ws + off_pooled + (size_t)img0 * tt.c * 4;
     const dml::Buf& b = net.bufs[tt.buf];
     return ws + off_arena + ((size_t)b.offset * micro_batch + tt.c_off) * act_bytes;
@@ -115,6 +115,35 @@ namespace {
 int check_model(int model) {
   if (model != DML_MODEL_RESNET50 && model != DML_MODEL_INCEPTIONV3)
     return fail(DML_EINVAL, "unknown model id %d (0 = ResNet50, 1 = InceptionV3)", model);
+  return 0;
+}
+
+// The stem as the stride-1 conv over the space-to-depth input that the halo kernel runs.
+dml::ConvParams stem_s2d_params(const dml_engine* e, int img0, int cnt) {
+  const dml::Net& net = e->net;
+  const dml::Op& op = net.ops[net.s2d.op];
+  const dml::Tensor& to = net.tensors[op.out];
+  dml::ConvParams p{};
+  p.in = e->ws + e->off_input;          // whole input tensor; in_img0 selects the image
+  p.in_img0 = img0;
+  p.w = e->wts + net.s2d.w_off;
+  p.bias = reinterpret_cast<const float*>(e->wts + op.bias_off);
+  p.out = e->tensor_ptr(op.out, 0);
+  p.out_row0 = 0;
+  p.n = cnt; p.hi = net.s2d.size; p.wi = net.s2d.size; p.cin = 16; p.in_pitch = 16; p.cin_pad = 16;
+  p.ho = to.h; p.wo = to.w; p.cout = op.cout; p.out_pitch = to.c_pitch;
+  p.kh = net.s2d.k2; p.kw = net.s2d.k2; p.stride = 1; p.pad_h = net.s2d.pad2; p.pad_w = net.s2d.pad2;
+  p.relu = op.relu;
+  return p;
+}
+
+int plan_stem(dml_engine* e) {
+  if (!e->s2d) return 0;
+  dml::TcTune tune;
+  tune.version = 6;
+  dml::ConvParams p = stem_s2d_params(e, 0, e->micro_batch);
+  if (dml::tc_plan_one(&e->stem_plan, p, e->max_batch, tune) != 0)
+    return fail(DML_ECUDA, "space-to-depth stem plan failed: %s", dml::tc_last_error());
   return 0;
 }
 
@@ -138,7 +167,12 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
       p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;
       p.cin_pad = op.cin_pad; p.relu = op.relu;
       int nl = 0;
-      if (e->use_tc && dml::tc_supported(op)) {
+      if (e->s2d && (int)oi == net.s2d.op) {
+        dml::ConvParams p2 = stem_s2d_params(e, img0, cnt);
+        if (dml::launch_conv_tc_plan(e->stem_plan, p2, s) != 0)
+          return fail(DML_ECUDA, "stem conv launch failed for %s: %s", op.name.c_str(), dml::tc_last_error());
+        nl = 1;
+      } else if (e->use_tc && dml::tc_supported(op)) {
         int rc = dml::launch_conv_tc(e->tc, (int)oi, p, img0, s, &nl);
         if (rc != 0) return fail(DML_ECUDA, "tcgen05 conv launch failed for %s: %s", op.name.c_str(), dml::tc_last_error());
       } else if (e->use_tc && dml::stem_tc_supported(p)) {
@@ -199,6 +233,7 @@ int run_pre(dml_engine* e, const uint8_t* d_pixels, const int64_t* d_img_off, co
   p.out = e->tensor_ptr(e->net.input_tensor, 0);
   p.n = img0 + cnt; p.S = S; p.caffe = e->net.mode == 0;
   p.img_begin = img0; p.img_end = img0 + cnt;
+  p.s2d = e->s2d ? 1 : 0;
   dml::launch_preprocess(p, reinterpret_cast<const float*>(e->ws + e->off_lut), e->fp32, s);
   e->launches += 1;
   CUDA_TRY(cudaGetLastError());
@@ -293,7 +328,9 @@ int dml_create(int device, int model, int max_batch, int micro_batch, int flags,
   const dml::Net& net = e->net;
   size_t off = 0;
   e->off_lut = off; off = align_up(off + 768 * 4, 256);
-  e->off_input = off; off = align_up(off + (size_t)max_batch * net.input_size * net.input_size * 3 * e->act_bytes + 64, 256);
+  e->s2d = e->use_tc && net.s2d.op >= 0 && getenv("DML_NO_S2D") == nullptr;
+  e->input_img_bytes = e->s2d ? (size_t)net.s2d.size * net.s2d.size * 16 * 2 : (size_t)net.input_size * net.input_size * 3 * e->act_bytes;
+  e->off_input = off; off = align_up(off + (size_t)max_batch * e->input_img_bytes + 64, 256);
   e->off_arena = off; off = align_up(off + (size_t)net.arena_elems * e->micro_batch * e->act_bytes, 256);
   e->off_pooled = off; off = align_up(off + (size_t)max_batch * net.tensors[net.pooled_tensor].c * 4, 256);
   e->off_logits = off; off = align_up(off + (size_t)max_batch * 1000 * 4, 256);
@@ -339,6 +376,7 @@ int dml_bind_workspace(dml_engine* e, void* dev_ptr, size_t bytes) {
   if (e->use_tc && e->wts) {
     if (dml::tc_plan(&e->tc, e->net, e->ws, e->off_arena, e->off_input, e->off_tc, e->wts, e->micro_batch, e->max_batch) != 0)
       return fail(DML_ECUDA, "tcgen05 plan failed: %s", dml::tc_last_error());
+    if (plan_stem(e) != 0) return DML_ECUDA;
   }
   return 0;
 }
@@ -355,6 +393,7 @@ int dml_bind_weights(dml_engine* e, void* dev_ptr, size_t bytes) {
     CUDA_TRY(cudaSetDevice(e->device));
     if (dml::tc_plan(&e->tc, e->net, e->ws, e->off_arena, e->off_input, e->off_tc, e->wts, e->micro_batch, e->max_batch) != 0)
       return fail(DML_ECUDA, "tcgen05 plan failed: %s", dml::tc_last_error());
+    if (plan_stem(e) != 0) return DML_ECUDA;
   }
   return 0;
 }
@@ -387,6 +426,17 @@ int dml_load_weights(dml_engine* e, const float* blob, size_t num_floats) {
           size_t idx = ((size_t)co * taps + t) * op.cin_pad + c;
           if (e->fp32) reinterpret_cast<float*>(host.data() + op.wpack_off)[idx] = v;
           else reinterpret_cast<uint16_t*>(host.data() + op.wpack_off)[idx] = f32_to_bf16_rn(v);
+          if (!e->fp32 && net.s2d.op >= 0 && &op == &net.ops[net.s2d.op]) {
+            // the same folded weight at its space-to-depth position: tap (r, s) reads pixel (2*oh + r - pad, ...)
+            // = cell (oh + a, ow + b), sub-pixel (py, px) with r - pad = 2a + py
+            const int r = t / op.kw, sx = t % op.kw;
+            const int dr = r - op.pad_h, ds = sx - op.pad_w;
+            const int a = dr >= 0 ? dr / 2 : -((-dr + 1) / 2), b = ds >= 0 ? ds / 2 : -((-ds + 1) / 2);
+            const int py = dr - 2 * a, px = ds - 2 * b;
+            const int tap2 = (a + net.s2d.pad2) * net.s2d.k2 + (b + net.s2d.pad2);
+            const size_t idx2 = ((size_t)co * net.s2d.k2 * net.s2d.k2 + tap2) * 16 + (size_t)((py * 2 + px) * 3 + c);
+            reinterpret_cast<uint16_t*>(host.data() + net.s2d.w_off)[idx2] = f32_to_bf16_rn(v);
+          }
         }
     }
   }
@@ -472,6 +522,14 @@ int dml_input_tensor(dml_engine* e, void** dev_ptr, int* elem_bytes) {
   if (!e->ws) return fail(DML_ESTATE, "no workspace bound");
   *dev_ptr = e->ws + e->off_input;
   if (elem_bytes) *elem_bytes = e->act_bytes;
+  return 0;
+}
+
+int dml_input_layout(dml_engine* e, int* layout, int* cells, int* cell_channels) {
+  if (!e || !layout) return fail(DML_EINVAL, "NULL argument");
+  *layout = e->s2d ? 1 : 0;
+  if (cells) *cells = e->s2d ? e->net.s2d.size : e->net.input_size;
+  if (cell_channels) *cell_channels = e->s2d ? 16 : 3;
   return 0;
 }
 

@@ -306,6 +306,20 @@ void plan_weights(Net* net, int wbytes, bool tc_pad) {
     op.bias_off = off;
     off = align_up(off + (int64_t)op.cout * 4, 256);
   }
+  // floor division by 2 of (tap - pad): cells a in [a_min, a_max] of the space-to-depth grid
+  auto fdiv2 = [](int v) { return v >= 0 ? v / 2 : -((-v + 1) / 2); };
+  if (tc_pad && !net->ops.empty()) {
+    const Op& st = net->ops[0];
+    if (st.kind == OP_CONV && st.cin == 3 && st.stride == 2 && st.kh == st.kw && st.pad_h == st.pad_w) {
+      const int a_min = fdiv2(-st.pad_h), a_max = fdiv2(st.kh - 1 - st.pad_h);
+      net->s2d.op = 0;
+      net->s2d.size = (net->input_size + 1) / 2;
+      net->s2d.k2 = a_max - a_min + 1;
+      net->s2d.pad2 = -a_min;
+      net->s2d.w_off = off;
+      off = align_up(off + (int64_t)st.cout * net->s2d.k2 * net->s2d.k2 * 16 * 2, 256);
+    }
+  }
   const WeightArr& fk = net->warr[net->fc_kernel];
   net->fc_w_off = off;
   off = align_up(off + fk.count * 4, 256);

@@ -64,6 +64,15 @@ struct Net {
   int64_t arena_elems = 0;             // per image
   int64_t weights_bytes = 0;
   int64_t conv_macs = 0;               // per image
+  // Space-to-depth form of the C_in = 3 stride-2 stem (bf16 tensor-core mode only): the S x S x 3 input is stored as
+  // S2 x S2 x 16 (channel (py*2+px)*3 + c = pixel (2y+py, 2x+px), channels 12..15 zero) and the k x k stride-2 filter
+  // becomes a k2 x k2 stride-1 filter over it whose first tap sits pad2 cells before the output position.
+  struct S2d {
+    int op = -1;             // index of the stem op, -1 = none
+    int size = 0;            // S2 = ceil(S / 2)
+    int k2 = 0, pad2 = 0;
+    int64_t w_off = 0;       // packed bf16 [cout][k2*k2][16], bytes into the weights buffer
+  } s2d;
 };
 
 // Builds the graph.  keep_all: every tensor gets its own storage (parity taps).

@@ -88,6 +88,47 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p, const floa
   }
 }
 
+// K1, space-to-depth flavour: one thread per output cell (y2, x2) = the 2x2 pixel block at (2*y2, 2*x2); 12 values
+// (sub-pixel-major, then channel) + 4 zero channels = 32 bytes.  Same gather + LUT as above, so the values are the
+// bf16 roundings of exactly the same fp32 numbers; pixels past the image edge (odd S) are zeros.
+__global__ void __launch_bounds__(256) preprocess_s2d_kernel(PreParams p, const float* __restrict__ lut_g, int caffe) {
+  __shared__ float lut[768];
+  for (int i = threadIdx.x; i < 768; i += blockDim.x) lut[i] = lut_g[i];
+  __syncthreads();
+  const int S = p.S, S2 = (S + 1) >> 1;
+  const int64_t cells = (int64_t)(p.img_end - p.img_begin) * S2 * S2;
+  const int64_t cell = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (cell >= cells) return;
+  const int img = p.img_begin + (int)(cell / (S2 * S2));
+  const int rem = (int)(cell - (int64_t)(img - p.img_begin) * S2 * S2);
+  const int y2 = rem / S2, x2 = rem - y2 * S2;
+  const uint8_t* src = p.pixels + p.img_off[img];
+  const int W = p.hw[2 * img + 1];
+  __nv_bfloat16 vals[16];
+#pragma unroll
+  for (int i = 12; i < 16; ++i) vals[i] = __float2bfloat16_rn(0.f);
+#pragma unroll
+  for (int py = 0; py < 2; ++py) {
+    const int y = 2 * y2 + py;
+    const int sy = y < S ? p.ytab[img * S + y] : 0;
+#pragma unroll
+    for (int px = 0; px < 2; ++px) {
+      const int x = 2 * x2 + px;
+      const bool in = y < S && x < S;
+      const int sx = x < S ? p.xtab[img * S + x] : 0;
+      const uint8_t* px_src = src + ((int64_t)sy * W + sx) * 3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const int sc = caffe ? 2 - c : c;
+        vals[(py * 2 + px) * 3 + c] = __float2bfloat16_rn(in ? lut[c * 256 + px_src[sc]] : 0.f);
+      }
+    }
+  }
+  uint4* out = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + ((int64_t)img * S2 * S2 + rem) * 16);
+  out[0] = reinterpret_cast<uint4*>(vals)[0];
+  out[1] = reinterpret_cast<uint4*>(vals)[1];
+}
+
 // ---------------------------------------------------------------------------
 // CUDA-core direct convolution: 64 pixels x 64 output channels per block,
 // 4x4 outputs per thread, K = taps*Cin walked in chunks of 16.
@@ -478,6 +519,13 @@ __global__ void __launch_bounds__(256) softmax_top5_kernel(const float* __restri
 }  // namespace
 
 void launch_preprocess(const PreParams& p, const float* d_lut, bool fp32_out, cudaStream_t s) {
+  if (p.s2d) {
+    const int S2 = (p.S + 1) / 2;
+    const int64_t cells = (int64_t)(p.img_end - p.img_begin) * S2 * S2;
+    if (cells <= 0) return;
+    preprocess_s2d_kernel<<<(unsigned)((cells + 255) / 256), 256, 0, s>>>(p, d_lut, p.caffe);
+    return;
+  }
   int64_t per_img = (int64_t)p.S * p.S * 3;
   int64_t lo = per_img * p.img_begin, hi = per_img * p.img_end;
   int64_t threads = (hi - (lo / 8) * 8 + 7) / 8;

@@ -37,6 +37,7 @@ struct PreParams {
   int n, S;             // n = images in the tensor the tables cover
   int img_begin, img_end;  // images [img_begin, img_end) are produced by this launch
   int caffe;            // 1: output channel c reads source channel 2-c (RGB->BGR)
+  int s2d;              // 1: bf16 space-to-depth output [n][S2][S2][16], S2 = (S+1)/2 (graph.h, Net::S2d)
 };
 
 // K1: NEAREST resize (host-computed index tables) + preprocess LUT; bf16 or fp32 out.

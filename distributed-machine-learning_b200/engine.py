@@ -244,6 +244,14 @@ class Engine:
         p, eb = C.c_void_p(), C.c_int()
         _lib.check(self.l.dml_input_tensor(self.h, C.byref(p), C.byref(eb)))
         off = p.value - self.workspace.data_ptr()
+        layout, cells, cch = C.c_int(), C.c_int(), C.c_int()
+        _lib.check(self.l.dml_input_layout(self.h, C.byref(layout), C.byref(cells), C.byref(cch)))
+        if layout.value == 1:
+            # space-to-depth cells [n][S2][S2][(py, px, c) + 4 zero channels] -> the [n][S][S][3] picture
+            s2 = cells.value
+            raw = self.workspace[off:off + n * s2 * s2 * 16 * 2].view(torch.bfloat16).view(n, s2, s2, 16)
+            pic = raw[..., :12].reshape(n, s2, s2, 2, 2, 3).permute(0, 1, 3, 2, 4, 5).reshape(n, 2 * s2, 2 * s2, 3)
+            return pic[:, :self.size, :self.size].contiguous()
         nbytes = n * self.size * self.size * 3 * eb.value
         raw = self.workspace[off:off + nbytes]
         dt = torch.float32 if eb.value == 4 else torch.bfloat16

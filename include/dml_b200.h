@@ -126,6 +126,13 @@ int dml_tensor_info(dml_engine* e, int i, char* name, int name_cap, int* h, int*
 
 /* The engine's preprocessed input tensor: n x S x S x 3 (bf16, or fp32 in check mode). */
 int dml_input_tensor(dml_engine* e, void** dev_ptr, int* elem_bytes);
+/* How K1 lays the input tensor out.  layout 0: [n][S][S][3] (what preprocess_input
+ * returns, models.py:37/:62).  layout 1 (bf16 tensor-core engines): space-to-depth
+ * [n][S2][S2][16] bf16 with S2 = ceil(S/2); channel (py*2+px)*3 + c of cell
+ * (y2, x2) is channel c of pixel (2*y2+py, 2*x2+px), channels 12..15 and pixels past
+ * the edge are zero -- the form in which the stride-2 stem convolution is a
+ * stride-1 convolution.  cells = S or S2, cell_channels = 3 or 16. */
+int dml_input_layout(dml_engine* e, int* layout, int* cells, int* cell_channels);
 
 /* Logits (pre-softmax), n x 1000 fp32, valid after dml_forward / dml_infer. */
 int dml_logits(dml_engine* e, float** dev_ptr);

@@ -272,6 +272,9 @@ RESIDENT_HALO_CASES = [
     (2, 17, 17, 24, 48, 1, 7, 1, 0, 3, False, False, 8, 16),       # 1x7, ragged 64-byte rows
     (2, 17, 17, 96, 48, 7, 1, 1, 3, 0, True, False, 0, 0),         # 7x1, two channel blocks, Cout 48
     (2, 30, 30, 128, 32, 3, 3, 1, 1, 1, True, False, 0, 0),        # 3x3 with two channel blocks (compile-time path)
+    (3, 112, 112, 16, 64, 4, 4, 1, 2, 2, True, False, 0, 0),       # 32-byte rows: the space-to-depth ResNet50 stem's shape
+    (2, 150, 150, 16, 32, 2, 2, 1, 0, 0, True, False, 0, 0),       # 32-byte rows, 2x2 valid: the InceptionV3 stem's shape
+    (2, 21, 21, 8, 48, 3, 3, 1, 1, 1, False, False, 8, 0),         # 32-byte rows, generic path, ragged channels
 ]
 
 
