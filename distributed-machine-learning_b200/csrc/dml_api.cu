@@ -211,7 +211,7 @@ int run_head(dml_engine* e, int n, float* d_probs, int32_t* d_idx, float* d_prob
   int cin = net.tensors[net.pooled_tensor].c;
   e->prof_begin((int)net.ops.size(), s);
   dml::launch_fc(pooled, reinterpret_cast<const float*>(e->wts + net.fc_w_off),
-                 reinterpret_cast<const float*>(e->wts + net.fc_b_off), logits, n, cin, s);
+                 reinterpret_cast<const float*>(e->wts + net.fc_b_off), logits, n, cin, !e->fp32, s);
   e->prof_end(s);
   e->prof_begin((int)net.ops.size() + 1, s);
   dml::launch_softmax_top5(logits, d_probs, d_idx, d_prob, n, s);

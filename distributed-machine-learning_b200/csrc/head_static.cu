@@ -64,7 +64,7 @@ extern "C" int dml_head_static(const float* d_pooled, const float* d_dense_w, co
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // Rows [0, n) of the scratch are fully rewritten by the dense kernel before the softmax kernel
   // reads them; nothing in it has to start at zero.
-  dml::launch_fc(d_pooled, d_dense_w, d_dense_b, scratch, n, cin, s);
+  dml::launch_fc(d_pooled, d_dense_w, d_dense_b, scratch, n, cin, true, s);  // the default (bf16) engines' dense kernel
   dml::launch_softmax_top5(scratch, d_probs, d_top5_idx, d_top5_prob, n, s);
   ce = cudaGetLastError();
   if (ce != cudaSuccess) return dml_set_error(DML_ECUDA, cudaGetErrorString(ce));

@@ -578,11 +578,100 @@ void launch_gap(const void* in, float* out, int n, int hw, int c, int in_pitch, 
   else gap_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(in), out, n, hw, c, in_pitch);
 }
 
-void init_kernels() {
-  cudaFuncSetAttribute(fc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+// Dense layer of the bf16 engines: logits = pooled x W + b as a TF32 tensor-core GEMM (mma.sync m16n8k8, fp32
+// accumulate).  A 256 x 2048 x 1000 product is too small for a tcgen05 pipeline to pay off and the fp32 CUDA-core
+// kernel above re-reads W once per 8 images; here a CTA owns 32 images x 64 classes and streams K in chunks of 32
+// through a cp.async double buffer.  The fp32 check mode keeps the exact fp32 kernel.
+constexpr int FT_BM = 32, FT_BN = 64, FT_BK = 32, FT_APAD = 36, FT_BPAD = 72, FT_STAGES = 5;
+constexpr size_t FT_SMEM = (size_t)FT_STAGES * (FT_BM * FT_APAD + FT_BK * FT_BPAD) * sizeof(float);
+__device__ __forceinline__ uint32_t to_tf32(float v) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return r;
+}
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc, bool pred) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  const int bytes = pred ? 16 : 0;  // 0 source bytes: the 16 destination bytes are zero filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(bytes) : "memory");
+}
+__global__ void __launch_bounds__(128) fc_tf32_kernel(const float* __restrict__ pooled, const float* __restrict__ w,
+                                                      const float* __restrict__ b, float* __restrict__ logits, int n, int cin) {
+  extern __shared__ __align__(16) float ft_smem[];
+  float (*As)[FT_BM][FT_APAD] = reinterpret_cast<float (*)[FT_BM][FT_APAD]>(ft_smem);
+  float (*Bs)[FT_BK][FT_BPAD] = reinterpret_cast<float (*)[FT_BK][FT_BPAD]>(ft_smem + FT_STAGES * FT_BM * FT_APAD);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, t = lane & 3;
+  const int m0 = blockIdx.x * FT_BM, n0 = blockIdx.y * FT_BN;
+  const int wm = (warp & 1) * 16, wn = (warp >> 1) * 32;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  auto load_stage = [&](int st, int k0) {
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {  // A: 32 rows x 8 float4
+      const int idx = tid + i * 128, r = idx >> 3, c4 = (idx & 7) * 4;
+      const bool ok = m0 + r < n;
+      cp_async16(&As[st][r][c4], pooled + (int64_t)(ok ? m0 + r : 0) * cin + k0 + c4, ok);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {  // B: 32 k rows x 16 float4
+      const int idx = tid + i * 128, r = idx >> 4, c4 = (idx & 15) * 4;
+      const bool ok = n0 + c4 < 1000;
+      cp_async16(&Bs[st][r][c4], w + (int64_t)(k0 + r) * 1000 + (ok ? n0 + c4 : 0), ok);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  const int nk = cin / FT_BK;
+  // FT_STAGES - 1 chunks in flight (L2 latency, not bandwidth, bounds a CTA that waits for every chunk)
+  for (int i = 0; i < FT_STAGES - 1; ++i) {
+    if (i < nk) load_stage(i, i * FT_BK);
+    else asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  for (int kc = 0; kc < nk; ++kc) {
+    const int st = kc % FT_STAGES;
+    asm volatile("cp.async.wait_group %0;" ::"n"(FT_STAGES - 2) : "memory");
+    __syncthreads();  // chunk kc has landed for everyone, and everyone is done with the stage refilled below
+    if (kc + FT_STAGES - 1 < nk) load_stage((kc + FT_STAGES - 1) % FT_STAGES, (kc + FT_STAGES - 1) * FT_BK);
+    else asm volatile("cp.async.commit_group;" ::: "memory");
+#pragma unroll
+    for (int k8 = 0; k8 < FT_BK; k8 += 8) {
+      const uint32_t a0 = to_tf32(As[st][wm + g][k8 + t]), a1 = to_tf32(As[st][wm + g + 8][k8 + t]);
+      const uint32_t a2 = to_tf32(As[st][wm + g][k8 + t + 4]), a3 = to_tf32(As[st][wm + g + 8][k8 + t + 4]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t b0 = to_tf32(Bs[st][k8 + t][wn + j * 8 + g]), b1 = to_tf32(Bs[st][k8 + t + 4][wn + j * 8 + g]);
+        asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                     : "+f"(acc[j][0]), "+f"(acc[j][1]), "+f"(acc[j][2]), "+f"(acc[j][3])
+                     : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int col = n0 + wn + j * 8 + 2 * t;
+    if (col >= 1000) continue;
+    const float b0 = b[col], b1 = b[col + 1];
+    const int r0 = m0 + wm + g, r1 = r0 + 8;
+    if (r0 < n) *reinterpret_cast<float2*>(logits + (int64_t)r0 * 1000 + col) = make_float2(acc[j][0] + b0, acc[j][1] + b1);
+    if (r1 < n) *reinterpret_cast<float2*>(logits + (int64_t)r1 * 1000 + col) = make_float2(acc[j][2] + b0, acc[j][3] + b1);
+  }
 }
 
-void launch_fc(const float* pooled, const float* w, const float* b, float* logits, int n, int cin, cudaStream_t s) {
+void init_kernels() {
+  cudaFuncSetAttribute(fc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+  cudaFuncSetAttribute(fc_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FT_SMEM);
+}
+
+void launch_fc(const float* pooled, const float* w, const float* b, float* logits, int n, int cin, bool tf32, cudaStream_t s) {
+  if (tf32 && cin % FT_BK == 0 && n > 0) {
+    dim3 grid((unsigned)((n + FT_BM - 1) / FT_BM), (1000 + FT_BN - 1) / FT_BN);
+    fc_tf32_kernel<<<grid, 128, FT_SMEM, s>>>(pooled, w, b, logits, n, cin);
+    return;
+  }
   dim3 grid((unsigned)((n + FC_IMGS - 1) / FC_IMGS), (1000 + FC_COLS - 1) / FC_COLS);
   size_t smem = (size_t)FC_IMGS * cin * sizeof(float);
   fc_kernel<<<grid, FC_WARPS * 32, smem, s>>>(pooled, w, b, logits, n, cin);

@@ -59,7 +59,8 @@ void launch_avgpool(const PoolParams& p, bool fp32_act, cudaStream_t s);
 void launch_gap(const void* in, float* out, int n, int hw, int c, int in_pitch, bool fp32_act, cudaStream_t s);
 
 // K7: Dense(1000) -> logits scratch; softmax + top-5.
-void launch_fc(const float* pooled, const float* w, const float* b, float* logits, int n, int cin, cudaStream_t s);
+// tf32: TF32 tensor-core GEMM (bf16 engines); otherwise the exact fp32 CUDA-core kernel (check mode).
+void launch_fc(const float* pooled, const float* w, const float* b, float* logits, int n, int cin, bool tf32, cudaStream_t s);
 // Per-device one-time kernel attribute set-up (call with the device current).
 void init_kernels();
 
