@@ -349,6 +349,7 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) conv_tc2_kernel(const __grid_c
                                                                  const __grid_constant__ CUtensorMap map_o,
                                                                  const __grid_constant__ CUtensorMap map_r,
                                                                  const TcV2Params p) {
+  pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int stages = p.stages;
@@ -394,6 +395,7 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) conv_tc2_kernel(const __grid_c
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+  pdl_wait();  // everything above overlapped the previous kernel's tail; its results are visible from here on
 
   if (warp == 0) {
     // ---------------- TMA producer (whole warp walks the loop, one elected lane issues) ----------------
@@ -930,6 +932,7 @@ template <int KH, int KW, int CBLOCKS, int ROW_BYTES>
 __global__ void __launch_bounds__(TC6_THREADS, 1) conv_tc6_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                  const __grid_constant__ CUtensorMap map_b,
                                                                  const TcV6Params p) {
+  pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int taps = p.kh * p.kw;
@@ -969,6 +972,7 @@ __global__ void __launch_bounds__(TC6_THREADS, 1) conv_tc6_kernel(const __grid_c
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+  pdl_wait();  // everything above overlapped the previous kernel's tail; its results are visible from here on
 
   if (warp == 0) {
     // ---------------- producer: the filter once, then one halo (all channel blocks) per tile ----------------
@@ -1218,6 +1222,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
     conv_tc2x_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                      const __grid_constant__ CUtensorMap map_o, const __grid_constant__ CUtensorMap map_r,
                      const TcV2Params p) {
+  pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int stages = p.stages;
@@ -1267,6 +1272,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+  pdl_wait();  // everything above overlapped the previous kernel's tail; its results are visible from here on
 
   if (warp == 0) {
     // ---------------- TMA producer (both CTAs): own 128 A rows, own half of the weight tile ----------------
@@ -1486,6 +1492,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc5_kernel(const __grid_co
                                                                  const __grid_constant__ CUtensorMap map_x,
                                                                  const __grid_constant__ CUtensorMap map_o,
                                                                  const TcV5Params p) {
+  pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int stages = p.stages;
@@ -1524,6 +1531,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc5_kernel(const __grid_co
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+  pdl_wait();  // everything above overlapped the previous kernel's tail; its results are visible from here on
 
   if (warp == 0) {
     // ---------------- TMA producer ----------------
@@ -2083,7 +2091,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     if (k.out_row0 + k.M > op.m_capacity) return tc_fail("batch of %d images exceeds the planned capacity", p.n);
     const int tiles = k.p_tiles * k.c_tiles;
     const int grid = tiles < g_num_sms ? tiles : g_num_sms;
-    conv_tc5_kernel<<<grid, TC_THREADS, op.smem, s>>>(op.map_b, op.map_a, op.map_o, k);
+    launch_pdl(conv_tc5_kernel, dim3(grid), dim3(TC_THREADS), op.smem, s, op.map_b, op.map_a, op.map_o, k);
     cudaError_t e5 = cudaGetLastError();
     if (e5 != cudaSuccess) return tc_fail("conv_tc5_kernel launch: %s", cudaGetErrorString(e5));
     return 0;
@@ -2113,17 +2121,17 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     static const bool prof6 = getenv("DML_TC_PROF") != nullptr;
     k.prof = prof6 ? 1 : 0;
     if (p.kh == 3 && p.kw == 3 && op.cpb == 1 && op.row_bytes == 128)
-      conv_tc6_kernel<3, 3, 1, 128><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+      launch_pdl(conv_tc6_kernel<3, 3, 1, 128>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
     else if (p.kh == 3 && p.kw == 3 && op.cpb == 1 && op.row_bytes == 64)
-      conv_tc6_kernel<3, 3, 1, 64><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+      launch_pdl(conv_tc6_kernel<3, 3, 1, 64>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
     else if (p.kh == 3 && p.kw == 3 && op.cpb == 2 && op.row_bytes == 128)
-      conv_tc6_kernel<3, 3, 2, 128><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+      launch_pdl(conv_tc6_kernel<3, 3, 2, 128>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
     else if (p.kh == 4 && p.kw == 4 && op.cpb == 1 && op.row_bytes == 32)
-      conv_tc6_kernel<4, 4, 1, 32><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+      launch_pdl(conv_tc6_kernel<4, 4, 1, 32>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
     else if (p.kh == 2 && p.kw == 2 && op.cpb == 1 && op.row_bytes == 32)
-      conv_tc6_kernel<2, 2, 1, 32><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+      launch_pdl(conv_tc6_kernel<2, 2, 1, 32>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
     else
-      conv_tc6_kernel<0, 0, 0, 0><<<grid, TC6_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
+      launch_pdl(conv_tc6_kernel<0, 0, 0, 0>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
     if (prof6) {
       cudaStreamSynchronize(s);
       static long long h[160 * 8];
@@ -2194,11 +2202,11 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     const int grid = tiles < g_num_sms ? tiles : g_num_sms;
     if (pair) {
       const int clusters = tiles < g_num_sms / 2 ? tiles : g_num_sms / 2;
-      conv_tc2x_kernel<<<2 * clusters, TC2_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
+      launch_pdl(conv_tc2x_kernel, dim3(2 * clusters), dim3(TC2_THREADS), op.smem, s, op.map_a, op.map_b, op.map_o, op.map_r, k);
     } else {
       static const bool prof = getenv("DML_TC_PROF") != nullptr;
       k.prof = prof ? 1 : 0;
-      conv_tc2_kernel<<<grid, TC2_THREADS, op.smem, s>>>(op.map_a, op.map_b, op.map_o, op.map_r, k);
+      launch_pdl(conv_tc2_kernel, dim3(grid), dim3(TC2_THREADS), op.smem, s, op.map_a, op.map_b, op.map_o, op.map_r, k);
       if (prof) {
         cudaStreamSynchronize(s);
         static long long h[160 * 8];

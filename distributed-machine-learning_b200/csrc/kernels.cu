@@ -8,6 +8,8 @@
 //                  (/root/reference/models.py:40-42, :65-67)
 #include "kernels.h"
 
+#include <cstdlib>
+
 #include <cuda_bf16.h>
 
 namespace dml {
@@ -24,6 +26,8 @@ template <> __device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float
 // ---------------------------------------------------------------------------
 template <typename TO>
 __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p, const float* __restrict__ lut_g, int caffe) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float lut[768];
   for (int i = threadIdx.x; i < 768; i += blockDim.x) lut[i] = lut_g[i];
   __syncthreads();
@@ -92,6 +96,8 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p, const floa
 // (sub-pixel-major, then channel) + 4 zero channels = 32 bytes.  Same gather + LUT as above, so the values are the
 // bf16 roundings of exactly the same fp32 numbers; pixels past the image edge (odd S) are zeros.
 __global__ void __launch_bounds__(256) preprocess_s2d_kernel(PreParams p, const float* __restrict__ lut_g, int caffe) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float lut[768];
   for (int i = threadIdx.x; i < 768; i += blockDim.x) lut[i] = lut_g[i];
   __syncthreads();
@@ -277,6 +283,8 @@ __global__ void __launch_bounds__(256) pool_kernel(PoolParams p) {
 // K4 fast path (bf16, 3x3): the nine 16-byte loads are issued back to back and reduced with packed
 // bf16x2 max (exact: max of bf16 values is a bf16 value); an out-of-bounds tap contributes 0.
 __global__ void __launch_bounds__(256) maxpool3_bf16_kernel(PoolParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int cg = p.c >> 3;
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (int64_t)p.n * p.ho * p.wo * cg) return;
@@ -321,6 +329,8 @@ __global__ void __launch_bounds__(256) maxpool3_bf16_kernel(PoolParams p) {
 constexpr int AVG_ROWS = 6;  // output rows per thread: more threads in flight than one thread per column
 template <typename T>
 __global__ void __launch_bounds__(256) avgpool3_kernel(PoolParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int V = Vec16<T>::N;
   const int cg = p.c / V;
   const int segs = (p.hi + AVG_ROWS - 1) / AVG_ROWS;
@@ -378,6 +388,8 @@ __global__ void __launch_bounds__(256) avgpool3_kernel(PoolParams p) {
 template <typename T>
 __global__ void __launch_bounds__(256) gap_kernel(const T* __restrict__ in, float* __restrict__ out, int n, int hw, int c,
                                                   int in_pitch) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int V = Vec16<T>::N;
   const int cg = c / V;
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -459,6 +471,8 @@ __global__ void __launch_bounds__(FC_WARPS * 32) fc_kernel(const float* __restri
 __global__ void __launch_bounds__(256) softmax_top5_kernel(const float* __restrict__ logits, float* __restrict__ probs,
                                                            int32_t* __restrict__ top_idx, float* __restrict__ top_prob,
                                                            int n) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float sp[1000];
   __shared__ float red[8];
   __shared__ int redi[8];
@@ -523,7 +537,7 @@ void launch_preprocess(const PreParams& p, const float* d_lut, bool fp32_out, cu
     const int S2 = (p.S + 1) / 2;
     const int64_t cells = (int64_t)(p.img_end - p.img_begin) * S2 * S2;
     if (cells <= 0) return;
-    preprocess_s2d_kernel<<<(unsigned)((cells + 255) / 256), 256, 0, s>>>(p, d_lut, p.caffe);
+    launch_pdl(preprocess_s2d_kernel, dim3((unsigned)((cells + 255) / 256)), dim3(256), 0, s, p, d_lut, p.caffe);
     return;
   }
   int64_t per_img = (int64_t)p.S * p.S * 3;
@@ -531,8 +545,8 @@ void launch_preprocess(const PreParams& p, const float* d_lut, bool fp32_out, cu
   int64_t threads = (hi - (lo / 8) * 8 + 7) / 8;
   if (threads <= 0) return;
   unsigned blocks = (unsigned)((threads + 255) / 256);
-  if (fp32_out) preprocess_kernel<float><<<blocks, 256, 0, s>>>(p, d_lut, p.caffe);
-  else preprocess_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(p, d_lut, p.caffe);
+  if (fp32_out) launch_pdl(preprocess_kernel<float>, dim3(blocks), dim3(256), 0, s, p, d_lut, p.caffe);
+  else launch_pdl(preprocess_kernel<__nv_bfloat16>, dim3(blocks), dim3(256), 0, s, p, d_lut, p.caffe);
 }
 
 void launch_conv_naive(const ConvParams& p, bool fp32_act, cudaStream_t s) {
@@ -553,7 +567,7 @@ static void launch_pool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
 void launch_maxpool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
   if (!fp32_act && p.k == 3) {
     int64_t total = (int64_t)p.n * p.ho * p.wo * (p.c / 8);
-    maxpool3_bf16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(p);
+    launch_pdl(maxpool3_bf16_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, s, p);
     return;
   }
   launch_pool<false>(p, fp32_act, s);
@@ -563,8 +577,8 @@ void launch_avgpool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
     int V = fp32_act ? 4 : 8;
     int64_t total = (int64_t)p.n * ((p.hi + AVG_ROWS - 1) / AVG_ROWS) * p.wi * (p.c / V);
     unsigned blocks = (unsigned)((total + 255) / 256);
-    if (fp32_act) avgpool3_kernel<float><<<blocks, 256, 0, s>>>(p);
-    else avgpool3_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(p);
+    if (fp32_act) launch_pdl(avgpool3_kernel<float>, dim3(blocks), dim3(256), 0, s, p);
+    else launch_pdl(avgpool3_kernel<__nv_bfloat16>, dim3(blocks), dim3(256), 0, s, p);
     return;
   }
   launch_pool<true>(p, fp32_act, s);
@@ -574,8 +588,8 @@ void launch_gap(const void* in, float* out, int n, int hw, int c, int in_pitch, 
   int V = fp32_act ? 4 : 8;
   int total = n * (c / V);
   unsigned blocks = (unsigned)((total + 255) / 256);
-  if (fp32_act) gap_kernel<float><<<blocks, 256, 0, s>>>(reinterpret_cast<const float*>(in), out, n, hw, c, in_pitch);
-  else gap_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(in), out, n, hw, c, in_pitch);
+  if (fp32_act) launch_pdl(gap_kernel<float>, dim3(blocks), dim3(256), 0, s, reinterpret_cast<const float*>(in), out, n, hw, c, in_pitch);
+  else launch_pdl(gap_kernel<__nv_bfloat16>, dim3(blocks), dim3(256), 0, s, reinterpret_cast<const __nv_bfloat16*>(in), out, n, hw, c, in_pitch);
 }
 
 // Dense layer of the bf16 engines: logits = pooled x W + b as a TF32 tensor-core GEMM (mma.sync m16n8k8, fp32
@@ -596,6 +610,8 @@ __device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc, b
 }
 __global__ void __launch_bounds__(128) fc_tf32_kernel(const float* __restrict__ pooled, const float* __restrict__ w,
                                                       const float* __restrict__ b, float* __restrict__ logits, int n, int cin) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ __align__(16) float ft_smem[];
   float (*As)[FT_BM][FT_APAD] = reinterpret_cast<float (*)[FT_BM][FT_APAD]>(ft_smem);
   float (*Bs)[FT_BK][FT_BPAD] = reinterpret_cast<float (*)[FT_BK][FT_BPAD]>(ft_smem + FT_STAGES * FT_BM * FT_APAD);
@@ -661,6 +677,11 @@ __global__ void __launch_bounds__(128) fc_tf32_kernel(const float* __restrict__ 
   }
 }
 
+bool pdl_enabled() {
+  static const bool on = getenv("DML_NO_PDL") == nullptr;
+  return on;
+}
+
 void init_kernels() {
   cudaFuncSetAttribute(fc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
   cudaFuncSetAttribute(fc_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FT_SMEM);
@@ -669,7 +690,7 @@ void init_kernels() {
 void launch_fc(const float* pooled, const float* w, const float* b, float* logits, int n, int cin, bool tf32, cudaStream_t s) {
   if (tf32 && cin % FT_BK == 0 && n > 0) {
     dim3 grid((unsigned)((n + FT_BM - 1) / FT_BM), (1000 + FT_BN - 1) / FT_BN);
-    fc_tf32_kernel<<<grid, 128, FT_SMEM, s>>>(pooled, w, b, logits, n, cin);
+    launch_pdl(fc_tf32_kernel, grid, dim3(128), FT_SMEM, s, pooled, w, b, logits, n, cin);
     return;
   }
   dim3 grid((unsigned)((n + FC_IMGS - 1) / FC_IMGS), (1000 + FC_COLS - 1) / FC_COLS);
@@ -678,7 +699,7 @@ void launch_fc(const float* pooled, const float* w, const float* b, float* logit
 }
 
 void launch_softmax_top5(const float* logits, float* probs, int32_t* top_idx, float* top_prob, int n, cudaStream_t s) {
-  softmax_top5_kernel<<<n, 256, 0, s>>>(logits, probs, top_idx, top_prob, n);
+  launch_pdl(softmax_top5_kernel, dim3((unsigned)n), dim3(256), 0, s, logits, probs, top_idx, top_prob, n);
 }
 
 }  // namespace dml

@@ -66,4 +66,31 @@ void init_kernels();
 
 void launch_softmax_top5(const float* logits, float* probs, int32_t* top_idx, float* top_prob, int n, cudaStream_t s);
 
+
+// ---- programmatic dependent launch (PDL) ----
+// Every kernel of a step is short (10-200 us) and fills the GPU by itself, so the launch latency and the prologue
+// (barrier init, TMEM allocation, tensor-map prefetch) of kernel i+1 are exposed after the tail of kernel i.  Kernels
+// launched through launch_pdl() may start while their predecessor drains; they call pdl_wait() before they touch any
+// memory a previous kernel may have written or may still read, and pdl_launch_dependents() at their start.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();  // false with DML_NO_PDL=1
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 }  // namespace dml
