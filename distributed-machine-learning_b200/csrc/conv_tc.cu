@@ -1214,6 +1214,51 @@ __device__ __forceinline__ void umma2_commit_both(uint32_t bar) {
                "h"((uint16_t)3)
                : "memory");
 }
+// Branch-free forms for the lean loops: every lane runs the instruction stream, elect.sync picks the one lane whose
+// predicate lets the TMA / MMA / commit through.  Without a C++ branch around them the operands stay warp-uniform
+// for the compiler (uniform registers, no R2UR / BSSY / BSYNC per k-block), which is what the single issuing warp's
+// time goes into otherwise (DML_TC_PROF: ~400-650 busy cycles per k-block against 256-512 cycles of MMA work).
+__device__ __forceinline__ void tma2_load_2d_elect(uint32_t dst, const CUtensorMap* map, uint32_t bar, int x, int y) {
+  asm volatile(
+      "{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\t"
+      "@P cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n\t}" ::"r"(dst),
+      "l"(map), "r"(bar & PEER_BIT_MASK), "r"(x), "r"(y)
+      : "memory");
+}
+__device__ __forceinline__ void tma2_load_im2col_4d_elect(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c, int w, int h,
+                                                          int n, uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\t"
+      "@P cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};\n\t}" ::"r"(dst),
+      "l"(map), "r"(bar & PEER_BIT_MASK), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+// four K = 16 steps of one 64-channel k-block; lo words of the descriptors advance by 2 (32 bytes) per step
+__device__ __forceinline__ void umma2_bf16_x4_elect(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                                    uint32_t accum_first) {
+  asm volatile(
+      "{\n\t.reg .pred P, Q;\n\t.reg .b64 da, db;\n\t.reg .b32 al, bl;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "setp.ne.b32 Q, %5, 0;\n\t"
+      "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+      "@P tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, Q;\n\t"
+      "add.u32 al, %1, 2;\n\tadd.u32 bl, %2, 2;\n\tmov.b64 da, {al, %3};\n\tmov.b64 db, {bl, %3};\n\t"
+      "@P tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, 1;\n\t"
+      "add.u32 al, %1, 4;\n\tadd.u32 bl, %2, 4;\n\tmov.b64 da, {al, %3};\n\tmov.b64 db, {bl, %3};\n\t"
+      "@P tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, 1;\n\t"
+      "add.u32 al, %1, 6;\n\tadd.u32 bl, %2, 6;\n\tmov.b64 da, {al, %3};\n\tmov.b64 db, {bl, %3};\n\t"
+      "@P tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, 1;\n\t}" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accum_first)
+      : "memory");
+}
+__device__ __forceinline__ void umma2_commit_both_elect(uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\t"
+      "@P tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}" ::"r"(bar),
+      "h"((uint16_t)3)
+      : "memory");
+}
 __device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & PEER_BIT_MASK) : "memory");
 }
@@ -1279,6 +1324,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
     const int howo = p.ho * p.wo;
     const uint32_t tx_bytes = 2u * A_STAGE_BYTES + 2u * b_half_bytes;
     uint32_t it = 0, lt = 0;
+    long long prof_pw = 0;
+    const long long prof_p0 = p.prof ? clock64() : 0;
     const uint32_t chunk_bytes = (uint32_t)BLOCK_M * (uint32_t)p.cw * 2u;
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
       const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
@@ -1303,20 +1350,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
         const int cnt = p.num_kb - j0 < G ? p.num_kb - j0 : G;
         const uint32_t s = it % (uint32_t)stages;
         const uint32_t ph = (it / (uint32_t)stages) & 1u;
+        const long long w0 = p.prof ? clock64() : 0;
         mbar_wait_spin(empty0 + 8u * s, ph ^ 1u);
+        if (p.prof) prof_pw += clock64() - w0;
         if (leader && elect_one()) mbar_arrive_expect_tx(full0 + 8u * s, (uint32_t)cnt * tx_bytes);
         __syncwarp();
         for (int g = 0; g < cnt; ++g) {
-          if (elect_one()) {
+          {
             const uint32_t sub = s * (uint32_t)G + (uint32_t)g;
             if (p.a_tiled)
-              tma2_load_2d(sA + sub * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, p.in_row0 + m0);
+              tma2_load_2d_elect(sA + sub * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, p.in_row0 + m0);
             else
-              tma2_load_im2col_4d(sA + sub * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base,
-                                  img + p.in_img0, (uint16_t)sx, (uint16_t)r);
-            tma2_load_2d(sB + sub * b_half_bytes, &map_b, full0 + 8u * s, (j0 + g) * BLOCK_K, n0 + (int)rank * (p.bn >> 1));
+              tma2_load_im2col_4d_elect(sA + sub * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base,
+                                        img + p.in_img0, (uint16_t)sx, (uint16_t)r);
+            tma2_load_2d_elect(sB + sub * b_half_bytes, &map_b, full0 + 8u * s, (j0 + g) * BLOCK_K, n0 + (int)rank * (p.bn >> 1));
           }
-          __syncwarp();
           if (++cb == p.cpb) {
             cb = 0;
             if (++sx == p.kw) { sx = 0; ++r; }
@@ -1324,14 +1372,24 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
         }
       }
     }
+    if (p.prof && leader && lane == 0) {
+      g_tc2_prof[cluster_id * 8 + 0] = prof_pw;
+      g_tc2_prof[cluster_id * 8 + 1] = clock64() - prof_p0;
+    }
   } else if (warp == 1) {
     if (leader) {
       // ---------------- MMA issuer (leader CTA only; warp-uniform loop, one elected lane issues) ----------------
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)((2 * BLOCK_M) >> 4) << 24);
       uint32_t it = 0, lt = 0;
+      const uint32_t desc_hi = (uint32_t)(make_sw128_desc(0) >> 32);
+      const uint32_t a_lo0 = (sA >> 4) | (1u << 16), b_lo0 = (sB >> 4) | (1u << 16);  // low word: address >> 4, LBO field = 1
+      long long prof_te = 0, prof_full = 0;
+      const long long prof_m0 = p.prof ? clock64() : 0;
       for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
         const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
+        const long long w1 = p.prof ? clock64() : 0;
         mbar_wait_spin(tempty0 + 8u * a, aph ^ 1u);  // both CTAs' epilogues have drained this accumulator
+        if (p.prof) prof_te += clock64() - w1;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
         int cb = 0;
@@ -1339,8 +1397,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
           const int cnt = p.num_kb - j0 < G ? p.num_kb - j0 : G;
           const uint32_t s = it % (uint32_t)stages;
           const uint32_t ph = (it / (uint32_t)stages) & 1u;
+          const long long w2 = p.prof ? clock64() : 0;
           mbar_wait_spin(full0 + 8u * s, ph);
+          if (p.prof) prof_full += clock64() - w2;
           tc_fence_after();
+          if (p.last_kmma == BLOCK_K / 16) {
+            // every k-block carries four K steps (Cin is a multiple of 64): lean, branch-free issue
+            for (int g = 0; g < cnt; ++g) {
+              const uint32_t sub = s * (uint32_t)G + (uint32_t)g;
+              umma2_bf16_x4_elect(d_tmem, a_lo0 + sub * (A_STAGE_BYTES >> 4), b_lo0 + sub * (b_half_bytes >> 4), desc_hi, idesc,
+                                  (uint32_t)((j0 | g) != 0));
+            }
+            umma2_commit_both_elect(empty0 + 8u * s);
+            continue;
+          }
           for (int g = 0; g < cnt; ++g) {
             const uint32_t sub = s * (uint32_t)G + (uint32_t)g;
             const uint64_t da = make_sw128_desc(sA + sub * A_STAGE_BYTES);
@@ -1359,6 +1429,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
         }
         if (elect_one()) umma2_commit_both(tfull0 + 8u * a);
         __syncwarp();
+      }
+      if (p.prof && lane == 0) {
+        g_tc2_prof[cluster_id * 8 + 2] = prof_te;
+        g_tc2_prof[cluster_id * 8 + 3] = prof_full;
+        g_tc2_prof[cluster_id * 8 + 4] = clock64() - prof_m0;
+        g_tc2_prof[cluster_id * 8 + 7] = lt;
       }
     }
   } else {
@@ -2199,10 +2275,23 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.n_tiles = p.cout / op.bn;
     k.cw = op.cw;
     const int tiles = k.m_tiles * k.n_tiles;
-    const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+    static const int sm_limit = getenv("DML_SM_LIMIT") ? atoi(getenv("DML_SM_LIMIT")) : g_num_sms;  // experiments: use fewer SMs
+    const int grid = tiles < sm_limit ? tiles : sm_limit;
     if (pair) {
-      const int clusters = tiles < g_num_sms / 2 ? tiles : g_num_sms / 2;
+      const int clusters = tiles < sm_limit / 2 ? tiles : sm_limit / 2;
+      static const bool profx = getenv("DML_TC_PROF") != nullptr;
+      k.prof = profx ? 1 : 0;
       launch_pdl(conv_tc2x_kernel, dim3(2 * clusters), dim3(TC2_THREADS), op.smem, s, op.map_a, op.map_b, op.map_o, op.map_r, k);
+      if (profx) {
+        cudaStreamSynchronize(s);
+        static long long h[160 * 8];
+        cudaMemcpyFromSymbol(h, g_tc2_prof, sizeof h);
+        double a[8] = {};
+        for (int b2 = 0; b2 < clusters; ++b2) for (int i = 0; i < 8; ++i) a[i] += (double)h[b2 * 8 + i];
+        const double kb = a[7] * k.num_kb;
+        fprintf(stderr, "[tc2x prof] bn %d group %d stages %d kb/tile %d tiles/cluster %.1f | cycles per k-block: producer total %.0f (wait empty %.0f) | mma total %.0f (wait full %.0f, wait tmem-empty %.0f)\n",
+                op.bn, op.group, op.stages, k.num_kb, a[7] / clusters, a[1] / kb, a[0] / kb, a[4] / kb, a[3] / kb, a[2] / kb);
+      }
     } else {
       static const bool prof = getenv("DML_TC_PROF") != nullptr;
       k.prof = prof ? 1 : 0;
