@@ -631,14 +631,12 @@ struct TcV3Params {
   int bn, n_tiles, relu;
   int tmem_cols, acc_stride, cw;
   int in_img0, out_img0;
-  int desc_mode;                // experiment: how the unaligned A start is described
 };
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-__device__ long long g_v3_dbg[160 * 8];
 
 __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                  const __grid_constant__ CUtensorMap map_b,
@@ -679,7 +677,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_co
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
-  long long acc_dbg[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // per-thread cycle counters (DML_V3_DESC_MODE), written once at the end
   // tile -> (image, first position, n tile); N tiles of one position range are adjacent
   auto decode = [&](int tile, int& img, int& l0, int& n0) {
     const int nt = tile % p.n_tiles;
@@ -698,9 +695,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_co
       const int row0 = l0 / p.wp;  // first padded row the tile touches
       for (int cb = 0; cb < p.cblocks; ++cb, ++ita) {
         const uint32_t sa = ita % (uint32_t)p.a_stages, pha = (ita / (uint32_t)p.a_stages) & 1u;
-        long long d0 = p.desc_mode ? clock64() : 0;
         mbar_wait(aempty0 + 8u * sa, pha ^ 1u);
-        if (p.desc_mode && lane == 0) acc_dbg[0] += clock64() - d0;
         if (elect_one()) {
           mbar_arrive_expect_tx(afull0 + 8u * sa, (uint32_t)p.rows_box * (uint32_t)p.wp * 128u);
           // 4D tiled box {64 ch, Wp, rows_box, 1} at (channel, -pad_w, row0 - pad_h, image): OOB -> zeros
@@ -713,9 +708,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_co
         __syncwarp();
         for (int t = 0; t < taps; ++t, ++itb) {
           const uint32_t sb = itb % (uint32_t)p.b_stages, phb = (itb / (uint32_t)p.b_stages) & 1u;
-          long long d1 = p.desc_mode ? clock64() : 0;
           mbar_wait(bempty0 + 8u * sb, phb ^ 1u);
-          if (p.desc_mode && lane == 0) acc_dbg[1] += clock64() - d1;
           if (elect_one()) {
             mbar_arrive_expect_tx(bfull0 + 8u * sb, b_stage_bytes);
             tma_load_2d(sB + sb * b_stage_bytes, &map_b, bfull0 + 8u * sb, (t * p.cblocks + cb) * BLOCK_K, n0);
@@ -733,25 +726,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_co
       decode(tile, img, l0, n0);
       const int loff = l0 - (l0 / p.wp) * p.wp;  // tile's first position inside the loaded rows
       const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
-      long long d2 = p.desc_mode ? clock64() : 0;
       mbar_wait(tempty0 + 8u * a, aph ^ 1u);
-      if (p.desc_mode && lane == 0) acc_dbg[2] += clock64() - d2;
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
       uint32_t first = 1;
       for (int cb = 0; cb < p.cblocks; ++cb, ++ita) {
         const uint32_t sa = ita % (uint32_t)p.a_stages, pha = (ita / (uint32_t)p.a_stages) & 1u;
-        long long d3 = p.desc_mode ? clock64() : 0;
         mbar_wait(afull0 + 8u * sa, pha);
-        if (p.desc_mode && lane == 0) acc_dbg[3] += clock64() - d3;
         tc_fence_after();
         const uint32_t a_base = sA + sa * (uint32_t)p.a_stage_bytes;
         int r = 0, sx = 0;
         for (int t = 0; t < taps; ++t, ++itb) {
           const uint32_t sb = itb % (uint32_t)p.b_stages, phb = (itb / (uint32_t)p.b_stages) & 1u;
-          long long d4 = p.desc_mode ? clock64() : 0;
           mbar_wait(bfull0 + 8u * sb, phb);
-          if (p.desc_mode && lane == 0) acc_dbg[4] += clock64() - d4;
           tc_fence_after();
           const uint32_t a_addr = a_base + (uint32_t)(loff + r * p.wp + sx) * 128u;
           // the swizzle is a function of the absolute shared-memory address, so a start that is only
@@ -793,9 +780,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_co
         if (hp < p.ho && wq < p.wo) off = (((img + p.out_img0) * p.ho + hp) * p.wo + wq) * p.out_pitch + n0;
         asm volatile("st.shared.b32 [%0], %1;" ::"r"(sOff + (lt & 1u) * 512u + (uint32_t)et * 4u), "r"(off) : "memory");
       }
-      long long d5 = (p.desc_mode && et == 0) ? clock64() : 0;
       mbar_wait(tfull0 + 8u * a, aph);
-      long long d6 = (p.desc_mode && et == 0) ? clock64() : 0;
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
       for (int c0 = 0; c0 < p.bn; c0 += cw, ++nchunk) {
@@ -854,12 +839,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_co
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty0 + 8u * a);
-      if (p.desc_mode && et == 0) { acc_dbg[5] += d6 - d5; acc_dbg[6] += clock64() - d6; acc_dbg[7] += 1; }
     }
-  }
-  if (p.desc_mode && (lane == 0)) {
-    for (int i = 0; i < 8; ++i)
-      if (acc_dbg[i]) g_v3_dbg[blockIdx.x * 8 + i] = acc_dbg[i];
   }
   tc_fence_before();
   __syncthreads();
@@ -1984,7 +1964,6 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
       op.cw = op.bn % 64 == 0 ? 64 : (op.bn % 32 == 0 ? 32 : 16);
       const int fixed = 1024 + 2 * 16384 + 1024 + 512;
       op.a_stages = op.cpb >= 2 ? 3 : 2;
-      if (const char* e = getenv("DML_V3_ASTAGES")) op.a_stages = atoi(e);
       int b_bytes = op.bn * 128;
       while (op.a_stages > 1 && fixed + op.a_stages * op.a_stage_bytes + 2 * b_bytes > SMEM_LIMIT) --op.a_stages;
       int room = SMEM_LIMIT - fixed - op.a_stages * op.a_stage_bytes;
@@ -1994,8 +1973,6 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
       if (op.b_stages >= 2) {
         op.smem = (size_t)fixed + (size_t)op.a_stages * op.a_stage_bytes + (size_t)op.b_stages * b_bytes;
         op.m_capacity = n_capacity;
-        static const char* dm = getenv("DML_V3_DESC_MODE");
-        op.desc_mode = dm ? atoi(dm) : 0;
         cuuint64_t gdim[4] = {(cuuint64_t)p.cin, (cuuint64_t)p.wi, (cuuint64_t)p.hi, (cuuint64_t)n_capacity};
         cuuint64_t gstr[3] = {(cuuint64_t)p.in_pitch * 2, (cuuint64_t)p.wi * p.in_pitch * 2, (cuuint64_t)p.hi * p.wi * p.in_pitch * 2};
         cuuint32_t box[4] = {BLOCK_K, (cuuint32_t)wp, (cuuint32_t)op.rows_box, 1};
@@ -2233,20 +2210,10 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.bn = op.bn; k.n_tiles = p.cout / op.bn; k.relu = p.relu;
     k.tmem_cols = op.tmem_cols; k.acc_stride = op.acc_stride; k.cw = op.cw;
     k.in_img0 = p.in_img0; k.out_img0 = 0;  // p.out already points at the launch's first image
-    k.desc_mode = op.desc_mode;
     if (p.in_img0 + p.n > op.m_capacity) return tc_fail("batch of %d images exceeds the planned capacity", p.n);
     const long long tiles = (long long)p.n * op.tiles_per_img * k.n_tiles;
     const int grid = tiles < g_num_sms ? (int)tiles : g_num_sms;
-    if (k.desc_mode) { static long long z[160 * 8] = {}; cudaMemcpyToSymbol(g_v3_dbg, z, sizeof z); }
     conv_tc3_kernel<<<grid, TC_THREADS, op.smem, s>>>(op.map_a, op.map_b, k);
-    if (k.desc_mode) {
-      static long long h[160 * 8];
-      cudaDeviceSynchronize();
-      cudaMemcpyFromSymbol(h, g_v3_dbg, sizeof h);
-      double a[8] = {};
-      for (int b2 = 0; b2 < grid; ++b2) for (int i = 0; i < 8; ++i) a[i] += (double)h[b2 * 8 + i];
-      fprintf(stderr, "[v3 dbg] bn %d a_stages %d b_stages %d tiles/cta %.1f | per tile: prod wait A-empty %.0f, B-empty %.0f | mma wait tempty %.0f, A-full %.0f, B-full %.0f | epi wait %.0f, work %.0f\n", op.bn, op.a_stages, op.b_stages, a[7] / grid, a[0] / a[7], a[1] / a[7], a[2] / a[7], a[3] / a[7], a[4] / a[7], a[5] / a[7], a[6] / a[7]);
-    }
     cudaError_t e3 = cudaGetLastError();
     if (e3 != cudaSuccess) return tc_fail("conv_tc3_kernel launch: %s", cudaGetErrorString(e3));
     return 0;

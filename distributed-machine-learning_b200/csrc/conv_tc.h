@@ -32,7 +32,6 @@ struct TcOpPlan {
   bool a_tiled = false;  // A fetched with a tiled 2D map (1x1 stride-1 convs)
   // v3 (halo kernel)
   int wp = 0, rows_box = 0, tiles_per_img = 0, q_valid = 0, a_stage_bytes = 0, a_stages = 0, b_stages = 0;
-  int desc_mode = 0;
   // v6 (halo kernel, resident filter)
   int a_cb_bytes = 0, row_bytes = 0;
 };

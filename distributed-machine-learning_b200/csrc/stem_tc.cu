@@ -34,7 +34,6 @@ struct StemParams {
   int tiles_x, tiles_y, total_tiles;
   int patch_h, patch_w, ppitch;  // input patch of one tile, row pitch in elements (even)
   int tmem_cols;
-  int dbg;
 };
 
 __device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -51,7 +50,6 @@ __device__ __forceinline__ uint32_t sw_chunk(int row, int k, int rows) {
   return (uint32_t)(kb * rows * 128 + row * 128 + ((j ^ (row & 7)) << 4));
 }
 
-__device__ long long g_stem_dbg[8];
 constexpr int STEM_BUILDERS = 256;                  // warps 0..7 build A tiles
 constexpr int STEM_THREADS_TOTAL = STEM_BUILDERS + 32 + 128;  // + MMA warp (8) + epilogue warps (9..12)
 
@@ -188,12 +186,10 @@ __global__ void __launch_bounds__(STEM_THREADS_TOTAL, 1) stem_tc_kernel(const __
         }
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");  // builders only
-      long long tb0 = (p.dbg && tid == 0) ? clock64() : 0;
       if (tile + (int)gridDim.x < p.total_tiles) fetch(tile + gridDim.x);  // loads fly during the expansion
       s_mbar_wait(aempty0 + 8u * buf, ph ^ 1u);  // the MMAs that read this A buffer two tiles ago have retired
-      long long tb1 = (p.dbg && tid == 0) ? clock64() : 0;
       // 2. expand: A[m][r*segpad .. +segpad) = patch[2ty + r][6tx .. +segpad)  (the tail past seg meets zero weights)
-      for (int i = tid; i < 128 * p.kh && !(p.dbg & 2); i += STEM_BUILDERS) {
+      for (int i = tid; i < 128 * p.kh; i += STEM_BUILDERS) {
         const int m = i & 127, r = i >> 7;
         const int ty = m >> 4, tx = m & 15;
         const uint32_t* src = reinterpret_cast<const uint32_t*>(patch + (2 * ty + r) * p.ppitch + 6 * tx);
@@ -207,7 +203,6 @@ __global__ void __launch_bounds__(STEM_THREADS_TOTAL, 1) stem_tc_kernel(const __
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
       if (lane == 0) s_mbar_arrive(afull0 + 8u * buf);
-      if (p.dbg && tid == 0 && blockIdx.x == 0) { long long t = clock64(); g_stem_dbg[0] += tb1 - tb0; g_stem_dbg[1] += t - tb1; g_stem_dbg[7] += 1; }
     }
   } else if (warp == 8) {
     // ---------------- MMA issuer: D[128 x cout] = A[128 x kpad] * B[cout x kpad]^T ----------------
@@ -216,11 +211,8 @@ __global__ void __launch_bounds__(STEM_THREADS_TOTAL, 1) stem_tc_kernel(const __
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
       const uint32_t buf = it & 1u, ph = (it >> 1) & 1u;
-      long long tm0 = (p.dbg && lane == 0) ? clock64() : 0;
       s_mbar_wait(tempty0 + 8u * buf, ph ^ 1u);  // the epilogue has drained this accumulator
-      long long tm1 = (p.dbg && lane == 0) ? clock64() : 0;
       s_mbar_wait(afull0 + 8u * buf, ph);
-      long long tm2 = (p.dbg && lane == 0) ? clock64() : 0;
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t a0 = base + buf * a_bytes;
       const uint32_t d_tmem = tmem_base + buf * (uint32_t)acc_cols;
@@ -239,7 +231,6 @@ __global__ void __launch_bounds__(STEM_THREADS_TOTAL, 1) stem_tc_kernel(const __
         s_commit(tfull0 + 8u * buf);
       }
       __syncwarp();
-      if (p.dbg && lane == 0 && blockIdx.x == 0) { long long t = clock64(); g_stem_dbg[2] += tm1 - tm0; g_stem_dbg[3] += tm2 - tm1; g_stem_dbg[4] += t - tm2; }
     }
   } else {
     // ---------------- epilogue: 4 warps = 128 tile rows, TMEM lane quarter = warp % 4 ----------------
@@ -251,9 +242,7 @@ __global__ void __launch_bounds__(STEM_THREADS_TOTAL, 1) stem_tc_kernel(const __
       const int img = tile / tiles_per_img;
       const int tr = tile - img * tiles_per_img;
       const int ty0 = (tr / p.tiles_x) * TILE_H, tx0 = (tr % p.tiles_x) * TILE_W;
-      long long te0 = (p.dbg && warp == 9 && lane == 0) ? clock64() : 0;
       s_mbar_wait(tfull0 + 8u * buf, ph);
-      long long te1 = (p.dbg && warp == 9 && lane == 0) ? clock64() : 0;
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)acc_cols;
       // the TMA store that read this staging buffer two tiles ago must be done reading it
@@ -262,7 +251,7 @@ __global__ void __launch_bounds__(STEM_THREADS_TOTAL, 1) stem_tc_kernel(const __
       const uint32_t row_bytes = (uint32_t)p.cout * 2u;  // 128 B (cout 64) or 64 B (cout 32)
       const uint32_t rowaddr = sO + buf * out_bytes + (uint32_t)m * row_bytes;
       const uint32_t swz = p.cout == 64 ? (uint32_t)(m & 7) : (uint32_t)((m >> 1) & 3);
-      for (int c0 = 0; c0 < p.cout && !(p.dbg & 4); c0 += 16) {
+      for (int c0 = 0; c0 < p.cout; c0 += 16) {
         uint32_t v[16];
         asm volatile(
             "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
@@ -302,7 +291,6 @@ __global__ void __launch_bounds__(STEM_THREADS_TOTAL, 1) stem_tc_kernel(const __
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
       if (lane == 0) s_mbar_arrive(tempty0 + 8u * buf);
-      if (p.dbg && warp == 9 && lane == 0 && blockIdx.x == 0) { long long t = clock64(); g_stem_dbg[5] += te1 - te0; g_stem_dbg[6] += t - te1; }
     }
     if (warp == 9 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
@@ -364,17 +352,7 @@ int launch_stem_tc(const ConvParams& c, cudaStream_t s) {
   if (per_sm < 1) per_sm = 1;
   int grid = num_sms * per_sm;
   if (grid > p.total_tiles) grid = p.total_tiles;
-  static const bool dbg = getenv("DML_STEM_DEBUG") != nullptr;
-  p.dbg = dbg ? atoi(getenv("DML_STEM_DEBUG")) : 0;
-  if (dbg) { long long z[8] = {}; cudaMemcpyToSymbol(g_stem_dbg, z, sizeof z); }
   stem_tc_kernel<<<grid, STEM_THREADS_TOTAL, smem, s>>>(map_o, p);
-  if (dbg) {
-    long long h[8];
-    cudaDeviceSynchronize();
-    cudaMemcpyFromSymbol(h, g_stem_dbg, sizeof h);
-    double t = (double)h[7];
-    fprintf(stderr, "[stem dbg] CTA0 tiles %.0f | per tile: builder wait A-empty %.0f, expand %.0f | mma wait t-empty %.0f, wait A-full %.0f, issue %.0f | epi wait %.0f, work %.0f\n", t, h[0] / t, h[1] / t, h[2] / t, h[3] / t, h[4] / t, h[5] / t, h[6] / t);
-  }
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
