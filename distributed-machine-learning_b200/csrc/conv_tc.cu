@@ -890,6 +890,7 @@ struct TcV6Params {
   int prof;
   int wide_store;  // output rows are 32-byte aligned: 256-bit stores
   int n_acc;       // TMEM accumulators (2 or 4)
+  int n_tiles;     // Cout / bn
   float inv_wp;    // 1 / wp
 };
 
@@ -931,6 +932,10 @@ __global__ void __launch_bounds__(TC6_THREADS, 1) conv_tc6_kernel(const __grid_c
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.n_img * p.tiles_per_img;
+  // Cout may be split into n_tiles slices when the whole filter does not fit: CTA c keeps slice c % n_tiles resident
+  // and walks the position tiles as virtual CTA c / n_tiles of gridDim.x / n_tiles
+  const int vcta = (int)blockIdx.x / p.n_tiles, vgrid = (int)gridDim.x / p.n_tiles;
+  const int n0 = ((int)blockIdx.x - vcta * p.n_tiles) * p.bn;
   long long prof[4] = {0, 0, 0, 0};  // DML_TC_PROF: producer wait empty | mma wait tmem-empty, wait A | epilogue wait accumulator
   const long long prof_t0 = p.prof ? clock64() : 0;
 
@@ -961,14 +966,14 @@ __global__ void __launch_bounds__(TC6_THREADS, 1) conv_tc6_kernel(const __grid_c
       mbar_arrive_expect_tx(bfull, (uint32_t)(taps * p.cblocks) * b_tile_bytes);
       for (int t = 0; t < taps; ++t)
         for (int cb = 0; cb < p.cblocks; ++cb)
-          tma_load_2d(sB + (uint32_t)(t * p.cblocks + cb) * b_tile_bytes, &map_b, bfull, t * p.cin_pad + cb * kb, 0);
+          tma_load_2d(sB + (uint32_t)(t * p.cblocks + cb) * b_tile_bytes, &map_b, bfull, t * p.cin_pad + cb * kb, n0);
     }
     __syncwarp();
     uint32_t ita = 0;
     const uint32_t box_bytes = (uint32_t)p.rows_box * (uint32_t)p.wp * row_bytes;
-    TileWalk tw(p.tiles_per_img, (int)blockIdx.x, (int)gridDim.x);
+    TileWalk tw(p.tiles_per_img, vcta, vgrid);
     uint32_t sa = 0, pha = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ita, tw.next(), pha ^= (++sa == (uint32_t)p.a_stages), sa = sa == (uint32_t)p.a_stages ? 0u : sa) {
+    for (int tile = vcta; tile < total_tiles; tile += vgrid, ++ita, tw.next(), pha ^= (++sa == (uint32_t)p.a_stages), sa = sa == (uint32_t)p.a_stages ? 0u : sa) {
       const int img = tw.img;
       const int l0 = tw.mt * BLOCK_M;
       const int row0 = div_wp(l0, p.inv_wp);  // first padded row the tile touches
@@ -993,9 +998,9 @@ __global__ void __launch_bounds__(TC6_THREADS, 1) conv_tc6_kernel(const __grid_c
     const int ksteps = p.row_bytes >> 5;
     mbar_wait(bfull, 0);
     uint32_t ita = 0;
-    TileWalk tw(p.tiles_per_img, (int)blockIdx.x, (int)gridDim.x);
+    TileWalk tw(p.tiles_per_img, vcta, vgrid);
     uint32_t sa = 0, pha = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ita, tw.next(), pha ^= (++sa == (uint32_t)p.a_stages), sa = sa == (uint32_t)p.a_stages ? 0u : sa) {
+    for (int tile = vcta; tile < total_tiles; tile += vgrid, ++ita, tw.next(), pha ^= (++sa == (uint32_t)p.a_stages), sa = sa == (uint32_t)p.a_stages ? 0u : sa) {
       const int l0 = tw.mt * BLOCK_M;
       const int loff = l0 - div_wp(l0, p.inv_wp) * p.wp;  // tile's first position inside the loaded rows
       const uint32_t a = ita & (n_acc - 1u), aph = (ita >> acc_shift) & 1u;
@@ -1072,21 +1077,21 @@ __global__ void __launch_bounds__(TC6_THREADS, 1) conv_tc6_kernel(const __grid_c
     const int et = q * 32 + lane;  // tile row
     const uint32_t sbias = sO;
     for (int c = (int)threadIdx.x - 64; c < p.bn; c += 256) {
-      const float bv = __ldg(p.bias + c);
+      const float bv = __ldg(p.bias + n0 + c);
       asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias + (uint32_t)c * 4u), "f"(bv) : "memory");
     }
     named_bar_sync(1, 256);
     const int g_begin = 0, g_end = p.bn;
     uint32_t lt = (uint32_t)grp;
-    TileWalk tw(p.tiles_per_img, (int)blockIdx.x + grp * (int)gridDim.x, 2 * (int)gridDim.x);
-    for (int tile = blockIdx.x + grp * gridDim.x; tile < total_tiles; tile += 2 * gridDim.x, lt += 2, tw.next()) {
+    TileWalk tw(p.tiles_per_img, vcta + grp * vgrid, 2 * vgrid);
+    for (int tile = vcta + grp * vgrid; tile < total_tiles; tile += 2 * vgrid, lt += 2, tw.next()) {
       const int img = tw.img;
       const int l0 = tw.mt * BLOCK_M;
       const uint32_t a = lt & (n_acc - 1u), aph = (lt >> acc_shift) & 1u;
       const int pos = l0 + et;
       const int hp = div_wp(pos, p.inv_wp), wq = pos - hp * p.wp;
       const bool valid = hp < p.ho && wq < p.wo;
-      const long long off = ((long long)((img + p.out_img0) * p.ho + hp) * p.wo + wq) * p.out_pitch;
+      const long long off = ((long long)((img + p.out_img0) * p.ho + hp) * p.wo + wq) * p.out_pitch + n0;
       const long long w4 = p.prof ? clock64() : 0;
       mbar_wait(tfull0 + 8u * a, aph);
       if (p.prof) prof[3] += clock64() - w4;
@@ -1774,12 +1779,13 @@ int tc_init() {
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc5_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
-  e = cudaFuncSetAttribute(conv_tc6_kernel<3, 3, 1, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<3, 3, 1, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<3, 3, 2, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<4, 4, 1, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<2, 2, 1, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<0, 0, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+#define DML_V6_SHAPES_INIT(X) X(3, 3, 1, 128) X(3, 3, 1, 64) X(3, 3, 2, 128) X(4, 4, 1, 32) X(2, 2, 1, 32) X(5, 5, 1, 128) \
+    X(1, 7, 2, 128) X(7, 1, 2, 128) X(1, 7, 3, 128) X(7, 1, 3, 128) X(1, 3, 6, 128) X(3, 1, 6, 128) X(0, 0, 0, 0)
+  e = cudaSuccess;
+#define DML_V6_ATTR(KH_, KW_, CB_, RB_) \
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<KH_, KW_, CB_, RB_>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  DML_V6_SHAPES_INIT(DML_V6_ATTR)
+#undef DML_V6_ATTR
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc6_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc3_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
@@ -1896,13 +1902,24 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
       v6.rows_box = (wp - 1 + BLOCK_M - 1 + halo) / wp + 1;
       v6.a_cb_bytes = (v6.rows_box * wp * row_bytes + 1023) / 1024 * 1024;
       v6.a_stage_bytes = cblocks * v6.a_cb_bytes;
-      v6.bn = p.cout;
+      // N tile: the whole Cout if its filter fits next to two halo stages, else the largest slice (Cout / 2, / 3, / 4) that does
+      int b_bytes = 0, fixed = 0;
+      v6.bn = 0;
+      for (int parts = 1; parts <= 4 && v6.bn == 0; ++parts) {
+        if (p.cout % parts || (p.cout / parts) % 16) continue;
+        if (tune.bn > 0 && p.cout / parts != tune.bn) continue;
+        const int bn = p.cout / parts;
+        b_bytes = (taps * cblocks * bn * row_bytes + 1023) / 1024 * 1024;
+        fixed = 1024 + b_bytes + bn * 4 + 16 + 512;
+        if ((SMEM_LIMIT - fixed) / v6.a_stage_bytes >= 2) v6.bn = bn;
+      }
+      if (v6.bn == 0) {
+        if (tune.version == 6) return tc_fail("resident-filter halo kernel does not fit in shared memory for this shape");
+      } else {
       v6.acc_stride = 32;
       while (v6.acc_stride < v6.bn) v6.acc_stride *= 2;
       v6.tmem_cols = v6.acc_stride <= 128 ? 4 * v6.acc_stride : 2 * v6.acc_stride;  // four accumulators when they fit
       v6.cw = v6.bn % 64 == 0 ? 64 : (v6.bn % 32 == 0 ? 32 : 16);
-      const int b_bytes = (taps * cblocks * v6.bn * row_bytes + 1023) / 1024 * 1024;
-      const int fixed = 1024 + b_bytes + v6.bn * 4 + 16 + 512;
       v6.a_stages = (SMEM_LIMIT - fixed) / v6.a_stage_bytes;
       if (v6.a_stages > 4) v6.a_stages = 4;
       if (tune.stages > 0 && tune.stages < v6.a_stages) v6.a_stages = tune.stages;
@@ -1932,6 +1949,7 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
         v6.valid = true;
         *out = v6;
         return 0;
+      }
       }
     }
   }
@@ -2166,25 +2184,27 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.last_kmma = (p.cin - (op.cpb - 1) * kb + 15) / 16;
     k.cin_pad = p.cin_pad;
     const int tiles = p.n * op.tiles_per_img;
-    const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+    k.n_tiles = p.cout / op.bn;
+    const int vgrid = tiles < g_num_sms / k.n_tiles ? tiles : g_num_sms / k.n_tiles;
+    const int grid = vgrid * k.n_tiles;
     k.n_acc = op.tmem_cols / op.acc_stride;
     k.inv_wp = 1.0f / (float)op.wp;
     k.wide_store = (p.out_pitch % 16 == 0 && reinterpret_cast<uintptr_t>(p.out) % 32 == 0 && !getenv("DML_NO_WIDE_STORE")) ? 1 : 0;
     if (getenv("DML_V6_NOSTORE")) k.wide_store = 2;  // experiment: skip the epilogue's global stores
     static const bool prof6 = getenv("DML_TC_PROF") != nullptr;
     k.prof = prof6 ? 1 : 0;
-    if (p.kh == 3 && p.kw == 3 && op.cpb == 1 && op.row_bytes == 128)
-      launch_pdl(conv_tc6_kernel<3, 3, 1, 128>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
-    else if (p.kh == 3 && p.kw == 3 && op.cpb == 1 && op.row_bytes == 64)
-      launch_pdl(conv_tc6_kernel<3, 3, 1, 64>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
-    else if (p.kh == 3 && p.kw == 3 && op.cpb == 2 && op.row_bytes == 128)
-      launch_pdl(conv_tc6_kernel<3, 3, 2, 128>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
-    else if (p.kh == 4 && p.kw == 4 && op.cpb == 1 && op.row_bytes == 32)
-      launch_pdl(conv_tc6_kernel<4, 4, 1, 32>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
-    else if (p.kh == 2 && p.kw == 2 && op.cpb == 1 && op.row_bytes == 32)
-      launch_pdl(conv_tc6_kernel<2, 2, 1, 32>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
-    else
-      launch_pdl(conv_tc6_kernel<0, 0, 0, 0>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
+    // compile-time shapes (fully unrolled MMA issue); anything else takes the generic loop
+#define DML_V6_SHAPES(X) X(3, 3, 1, 128) X(3, 3, 1, 64) X(3, 3, 2, 128) X(4, 4, 1, 32) X(2, 2, 1, 32) X(5, 5, 1, 128) \
+    X(1, 7, 2, 128) X(7, 1, 2, 128) X(1, 7, 3, 128) X(7, 1, 3, 128) X(1, 3, 6, 128) X(3, 1, 6, 128)
+    bool launched = false;
+#define DML_V6_TRY(KH_, KW_, CB_, RB_)                                                                                         \
+    if (!launched && p.kh == KH_ && p.kw == KW_ && op.cpb == CB_ && op.row_bytes == RB_) {                                       \
+      launch_pdl(conv_tc6_kernel<KH_, KW_, CB_, RB_>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);        \
+      launched = true;                                                                                                         \
+    }
+    DML_V6_SHAPES(DML_V6_TRY)
+#undef DML_V6_TRY
+    if (!launched) launch_pdl(conv_tc6_kernel<0, 0, 0, 0>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
     if (prof6) {
       cudaStreamSynchronize(s);
       static long long h[160 * 8];

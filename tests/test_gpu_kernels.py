@@ -275,6 +275,10 @@ RESIDENT_HALO_CASES = [
     (3, 112, 112, 16, 64, 4, 4, 1, 2, 2, True, False, 0, 0),       # 32-byte rows: the space-to-depth ResNet50 stem's shape
     (2, 150, 150, 16, 32, 2, 2, 1, 0, 0, True, False, 0, 0),       # 32-byte rows, 2x2 valid: the InceptionV3 stem's shape
     (2, 21, 21, 8, 48, 3, 3, 1, 1, 1, False, False, 8, 0),         # 32-byte rows, generic path, ragged channels
+    (3, 28, 28, 128, 128, 3, 3, 1, 1, 1, True, False, 0, 0),       # filter too big for one CTA: Cout split in 2 slices
+    (2, 35, 35, 48, 64, 5, 5, 1, 2, 2, True, False, 0, 32),        # 5x5, Cout split, concat slice
+    (2, 17, 17, 128, 128, 1, 7, 1, 0, 3, True, False, 0, 0),       # 1x7, two channel blocks, Cout split
+    (2, 17, 17, 128, 192, 7, 1, 1, 3, 0, False, False, 0, 576),    # 7x1, Cout 192 in 3 or 4 slices
 ]
 
 
