@@ -1528,6 +1528,244 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
 }
 
 
+// ------------- v6x: the resident-filter halo kernel on CTA PAIRS (cta_group::2, M = 256) -------------
+// For layers whose filter fits in the shared memory of TWO SMs: each CTA of a pair keeps HALF of the filter's
+// output channels resident and stages the halo of its own 128-position tile; the leader issues M = 256 MMAs over
+// both.  The two tiles of a pair must start at the same shared-memory offset (one descriptor serves both CTAs), so
+// tiles are ROW ALIGNED here: rpt = floor(128 / Wp) whole padded rows per CTA, first position at the start of the
+// box; the MMA rows past rpt * Wp compute garbage that is never stored.
+struct TcV6xParams {
+  const float* bias;
+  __nv_bfloat16* out;
+  int n_img, ho, wo, wp, out_pitch;
+  int kh, kw, pad_h, pad_w, cblocks;
+  int rpt, ptiles_per_img;       // output rows per CTA tile; pair tiles (2 * rpt rows) per image
+  int rows_box, a_cb_bytes, a_stage_bytes, a_stages;
+  int bn, n_tiles, relu, tmem_cols, acc_stride, n_acc;
+  int in_img0, out_img0;
+  int row_bytes, last_kmma, cin_pad, wide_store;
+  float inv_wp;
+};
+
+__device__ __forceinline__ void tma2_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar & PEER_BIT_MASK), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
+template <int KH, int KW, int CBLOCKS, int ROW_BYTES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC6_THREADS, 1)
+    conv_tc6x_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const TcV6xParams p) {
+  pdl_launch_dependents();
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int taps = p.kh * p.kw;
+  const uint32_t row_bytes = (uint32_t)p.row_bytes;
+  const uint32_t b_tile_bytes = (uint32_t)(p.bn >> 1) * row_bytes;       // this CTA's half of the N tile
+  const uint32_t sB = base;
+  const uint32_t sA = sB + (((uint32_t)(taps * p.cblocks) * b_tile_bytes + 1023u) & ~1023u);
+  const uint32_t sO = sA + (uint32_t)p.a_stages * (uint32_t)p.a_stage_bytes;  // bn biases (fp32)
+  const uint32_t bars = (sO + (uint32_t)p.bn * 4u + 15u) & ~15u;
+  const uint32_t afull0 = bars, aempty0 = afull0 + 8u * p.a_stages;
+  const uint32_t bfull = aempty0 + 8u * p.a_stages;
+  const uint32_t tfull0 = bfull + 8u, tempty0 = tfull0 + 32u;
+  const uint32_t tmem_slot = tempty0 + 32u;
+  const uint32_t n_acc = (uint32_t)p.n_acc;
+  const uint32_t acc_shift = n_acc == 4u ? 2u : 1u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int cl = (int)blockIdx.x >> 1, ncl = (int)gridDim.x >> 1;
+  const int vcl = cl / p.n_tiles, vn = ncl / p.n_tiles;        // Cout slice cl % n_tiles stays resident in this pair
+  const int n0 = (cl - vcl * p.n_tiles) * p.bn;
+  const int total_tiles = p.n_img * p.ptiles_per_img;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    for (int i = 0; i < p.a_stages; ++i) { mbar_init(afull0 + 8u * i, 1); mbar_init(aempty0 + 8u * i, 1); }
+    mbar_init(bfull, 1);
+    for (int i = 0; i < 4; ++i) { mbar_init(tfull0 + 8u * i, 1); mbar_init(tempty0 + 8u * i, 8); }  // leader: 4 warps of each CTA
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(p.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // both CTAs' barriers exist before anything remote touches them
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+  pdl_wait();
+
+  if (warp == 0) {
+    // ---------------- producer (both CTAs): own filter half once, then the halo of the own tile ----------------
+    const int kb = p.row_bytes >> 1;
+    if (elect_one()) {
+      if (leader) mbar_arrive_expect_tx(bfull, 2u * (uint32_t)(taps * p.cblocks) * b_tile_bytes);
+      for (int t = 0; t < taps; ++t)
+        for (int cb = 0; cb < p.cblocks; ++cb)
+          tma2_load_2d(sB + (uint32_t)(t * p.cblocks + cb) * b_tile_bytes, &map_b, bfull, t * p.cin_pad + cb * kb,
+                       n0 + (int)rank * (p.bn >> 1));
+    }
+    __syncwarp();
+    uint32_t ita = 0, sa = 0, pha = 0;
+    const uint32_t box_bytes = (uint32_t)p.rows_box * (uint32_t)p.wp * row_bytes;
+    TileWalk tw(p.ptiles_per_img, vcl, vn);
+    for (int tile = vcl; tile < total_tiles; tile += vn, ++ita, tw.next(), pha ^= (++sa == (uint32_t)p.a_stages), sa = sa == (uint32_t)p.a_stages ? 0u : sa) {
+      const int row0 = (tw.mt * 2 + (int)rank) * p.rpt;  // first output row of this CTA's tile (may be past the image: zero fill)
+      mbar_wait(aempty0 + 8u * sa, pha ^ 1u);
+      if (elect_one()) {
+        if (leader) mbar_arrive_expect_tx(afull0 + 8u * sa, 2u * (uint32_t)p.cblocks * box_bytes);
+        for (int cb = 0; cb < p.cblocks; ++cb)
+          tma2_load_4d(sA + sa * (uint32_t)p.a_stage_bytes + (uint32_t)cb * (uint32_t)p.a_cb_bytes, &map_a, afull0 + 8u * sa, cb * kb,
+                       -p.pad_w, row0 - p.pad_h, tw.img + p.in_img0);
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    if (leader) {
+      // ---------------- MMA issuer (leader only): no waits inside a tile ----------------
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)((2 * BLOCK_M) >> 4) << 24);
+      const int ksteps = p.row_bytes >> 5;
+      mbar_wait(bfull, 0);
+      uint32_t ita = 0, sa = 0, pha = 0;
+      for (int tile = vcl; tile < total_tiles; tile += vn, ++ita, pha ^= (++sa == (uint32_t)p.a_stages), sa = sa == (uint32_t)p.a_stages ? 0u : sa) {
+        const uint32_t a = ita & (n_acc - 1u), aph = (ita >> acc_shift) & 1u;
+        mbar_wait(tempty0 + 8u * a, aph ^ 1u);
+        mbar_wait(afull0 + 8u * sa, pha);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + a * (uint32_t)p.acc_stride;
+        const uint32_t a_base = sA + sa * (uint32_t)p.a_stage_bytes;
+        if (KH > 0) {
+          const uint64_t hi = make_sw_desc(0, (uint32_t)ROW_BYTES);
+          const uint32_t a_lo = a_base >> 4, b_lo = sB >> 4;
+          const uint32_t wp16 = ((uint32_t)p.wp * (uint32_t)ROW_BYTES) >> 4;
+          const uint32_t acb16 = (uint32_t)p.a_cb_bytes >> 4, bt16 = b_tile_bytes >> 4;
+          const int nk_last = p.last_kmma;
+          if (elect_one()) {
+#pragma unroll
+            for (int t = 0; t < KH * KW; ++t) {
+#pragma unroll
+              for (int cb = 0; cb < CBLOCKS; ++cb) {
+                const uint32_t ao = a_lo + (uint32_t)(t / KW) * wp16 + (uint32_t)((t % KW) * (ROW_BYTES >> 4)) + (uint32_t)cb * acb16;
+                const uint32_t bo = b_lo + (uint32_t)(t * CBLOCKS + cb) * bt16;
+#pragma unroll
+                for (int k = 0; k < ROW_BYTES / 32; ++k)
+                  if (cb < CBLOCKS - 1 || k < nk_last)
+                    umma2_bf16(d_tmem, hi | (uint64_t)((ao + 2u * k) & 0x3FFFu), hi | (uint64_t)((bo + 2u * k) & 0x3FFFu), idesc,
+                               (uint32_t)((t | cb | k) != 0));
+              }
+            }
+            umma2_commit_both(aempty0 + 8u * sa);
+            umma2_commit_both(tfull0 + 8u * a);
+          }
+          __syncwarp();
+          continue;
+        }
+        int r = 0, sx = 0;
+        for (int t = 0; t < taps; ++t) {
+          for (int cb = 0; cb < p.cblocks; ++cb) {
+            const uint64_t da = make_sw_desc(a_base + (uint32_t)cb * (uint32_t)p.a_cb_bytes + (uint32_t)(r * p.wp + sx) * row_bytes, row_bytes);
+            const uint64_t db = make_sw_desc(sB + (uint32_t)(t * p.cblocks + cb) * b_tile_bytes, row_bytes);
+            const int nk = (cb == p.cblocks - 1) ? p.last_kmma : ksteps;
+            if (elect_one()) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                if (k < nk) umma2_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((t | cb | k) != 0));
+            }
+            __syncwarp();
+          }
+          if (++sx == p.kw) { sx = 0; ++r; }
+        }
+        if (elect_one()) {
+          umma2_commit_both(aempty0 + 8u * sa);
+          umma2_commit_both(tfull0 + 8u * a);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ---------------- epilogue (both CTAs, own 128 rows): two groups of 4 warps drain alternate tiles ----------------
+    const int q = warp & 3;
+    const int grp = (warp - 2) >> 2;
+    const int et = q * 32 + lane;  // tile row = position et of the row-aligned tile
+    const uint32_t sbias = sO;
+    for (int c = (int)threadIdx.x - 64; c < p.bn; c += 256) {
+      const float bv = __ldg(p.bias + n0 + c);
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias + (uint32_t)c * 4u), "f"(bv) : "memory");
+    }
+    named_bar_sync(1, 256);
+    const int trow = div_wp(et, p.inv_wp), tcol = et - trow * p.wp;  // the same for every tile
+    uint32_t lt = (uint32_t)grp;
+    TileWalk tw(p.ptiles_per_img, vcl + grp * vn, 2 * vn);
+    for (int tile = vcl + grp * vn; tile < total_tiles; tile += 2 * vn, lt += 2, tw.next()) {
+      const uint32_t a = lt & (n_acc - 1u), aph = (lt >> acc_shift) & 1u;
+      const int orow = (tw.mt * 2 + (int)rank) * p.rpt + trow;
+      const bool valid = trow < p.rpt && orow < p.ho && tcol < p.wo;
+      const long long off = ((long long)((tw.img + p.out_img0) * p.ho + orow) * p.wo + tcol) * p.out_pitch + n0;
+      mbar_wait(tfull0 + 8u * a, aph);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
+      for (int g = 0; g < p.bn; g += 32) {
+        uint32_t v[2][16];
+        const bool two = g + 16 < p.bn;
+        tmem_ld16_nowait(t_row + (uint32_t)g, v[0]);
+        if (two) tmem_ld16_nowait(t_row + (uint32_t)(g + 16), v[1]);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          if (h == 1 && !two) break;
+          const int gg = g + 16 * h;
+          uint32_t pk[8];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float4 b4;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(b4.x), "=f"(b4.y), "=f"(b4.z), "=f"(b4.w)
+                         : "r"(sbias + (uint32_t)(gg + 4 * i) * 4u));
+            float f0 = __uint_as_float(v[h][4 * i + 0]) + b4.x, f1 = __uint_as_float(v[h][4 * i + 1]) + b4.y;
+            float f2 = __uint_as_float(v[h][4 * i + 2]) + b4.z, f3 = __uint_as_float(v[h][4 * i + 3]) + b4.w;
+            if (p.relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); f2 = fmaxf(f2, 0.f); f3 = fmaxf(f3, 0.f); }
+            __nv_bfloat162 lo = __floats2bfloat162_rn(f0, f1), hi = __floats2bfloat162_rn(f2, f3);
+            pk[2 * i] = *reinterpret_cast<uint32_t*>(&lo);
+            pk[2 * i + 1] = *reinterpret_cast<uint32_t*>(&hi);
+          }
+          if (valid) {
+            if (p.wide_store) {
+              asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p.out + off + gg), "r"(pk[0]), "r"(pk[1]),
+                           "r"(pk[2]), "r"(pk[3]), "r"(pk[4]), "r"(pk[5]), "r"(pk[6]), "r"(pk[7])
+                           : "memory");
+            } else {
+              uint4* dst = reinterpret_cast<uint4*>(p.out + off + gg);
+              dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_leader(tempty0 + 8u * a);  // the leader's MMA warp waits for both CTAs
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // the peer may still be reading this CTA's operands / arriving on its barriers
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+  }
+}
+
+
+#define DML_V6X_SHAPES(X) X(3, 3, 1, 128) X(3, 3, 2, 128) X(5, 5, 1, 128) X(1, 7, 2, 128) X(7, 1, 2, 128) X(1, 7, 3, 128) X(7, 1, 3, 128)
+
 // ------------- v5: "weights as A" for layers with few output channels -------------
 // A tcgen05.mma takes ~190 cycles on B200 whatever its N (measured), so with pixels on M (128 per
 // instruction) a Cout <= 128 layer can use at most N/256 of the tensor pipe.  Here the roles are
@@ -1779,6 +2017,12 @@ int tc_init() {
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc5_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
+  e = cudaSuccess;
+#define DML_V6X_ATTR(KH_, KW_, CB_, RB_) \
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6x_kernel<KH_, KW_, CB_, RB_>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  DML_V6X_SHAPES(DML_V6X_ATTR) DML_V6X_ATTR(0, 0, 0, 0)
+#undef DML_V6X_ATTR
+  if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc6x_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
 #define DML_V6_SHAPES_INIT(X) X(3, 3, 1, 128) X(3, 3, 1, 64) X(3, 3, 2, 128) X(4, 4, 1, 32) X(2, 2, 1, 32) X(5, 5, 1, 128) \
     X(1, 7, 2, 128) X(7, 1, 2, 128) X(1, 7, 3, 128) X(7, 1, 3, 128) X(1, 3, 6, 128) X(3, 1, 6, 128) X(0, 0, 0, 0)
   e = cudaSuccess;
@@ -1878,6 +2122,66 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
     if (r5 != CUDA_SUCCESS) return tc_fail("cuTensorMapEncodeTiled(output, weights-as-A) failed (%d): cout=%d cw=%d", (int)r5, p.cout, op.cw);
     op.valid = true;
     *out = op;
+    return 0;
+  }
+  // ---- v6x (version 7): the resident-filter halo kernel on CTA pairs, row-aligned tiles ----
+  if (tune.version == 7) {
+    const int wp = p.wo + p.kw - 1;
+    const int row_bytes = p.cin <= 16 ? 32 : (p.cin <= 32 ? 64 : 128);
+    const int kb = row_bytes / 2;
+    const int cblocks = (p.cin + kb - 1) / kb;
+    const int taps = p.kh * p.kw;
+    const bool eligible = p.stride == 1 && taps > 1 && p.res == nullptr && wp <= BLOCK_M && p.out != nullptr && p.cout % 16 == 0 &&
+                          p.cin % 8 == 0 && (p.in_pitch * 2) % 16 == 0 && (p.out_pitch * 2) % 16 == 0;
+    if (!eligible) return tc_fail("shape is not eligible for the pair resident-filter halo kernel");
+    TcOpPlan x = op;
+    x.version = 7;
+    x.wp = wp;
+    x.row_bytes = row_bytes;
+    x.cpb = cblocks;
+    x.rows_box = BLOCK_M / wp;                         // rpt: output rows per CTA tile (kept in rows_box; the box is rpt + kh - 1 rows)
+    x.tiles_per_img = (p.ho + 2 * x.rows_box - 1) / (2 * x.rows_box);  // pair tiles per image
+    const int box_rows = x.rows_box + p.kh - 1;
+    const int reach = BLOCK_M + (p.kh - 1) * wp + p.kw - 1;  // rows the shifted views of a 128-row MMA may touch
+    x.a_cb_bytes = ((box_rows * wp > reach ? box_rows * wp : reach) * row_bytes + 1023) / 1024 * 1024;
+    x.a_stage_bytes = cblocks * x.a_cb_bytes;
+    int fixed = 0;
+    x.bn = 0;
+    for (int parts = 1; parts <= 4 && x.bn == 0; ++parts) {
+      if (p.cout % parts || (p.cout / parts) % 16 || p.cout / parts > 256) continue;
+      if (tune.bn > 0 && p.cout / parts != tune.bn) continue;
+      const int bn = p.cout / parts;
+      const int b_bytes = (taps * cblocks * (bn / 2) * row_bytes + 1023) / 1024 * 1024;
+      fixed = 1024 + b_bytes + bn * 4 + 16 + 512;
+      if ((SMEM_LIMIT - fixed) / x.a_stage_bytes >= 1) x.bn = bn;
+    }
+    if (x.bn == 0 || box_rows > 256) return tc_fail("pair resident-filter halo kernel does not fit in shared memory for this shape");
+    x.acc_stride = 32;
+    while (x.acc_stride < x.bn) x.acc_stride *= 2;
+    x.tmem_cols = x.acc_stride <= 128 ? 4 * x.acc_stride : 2 * x.acc_stride;
+    x.a_stages = (SMEM_LIMIT - fixed) / x.a_stage_bytes;
+    if (x.a_stages > 4) x.a_stages = 4;
+    if (tune.stages > 0 && tune.stages < x.a_stages) x.a_stages = tune.stages;
+    x.smem = (size_t)fixed + (size_t)x.a_stages * x.a_stage_bytes;
+    x.m_capacity = n_capacity;
+    const CUtensorMapSwizzle sw = row_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (row_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+    cuuint64_t gdim[4] = {(cuuint64_t)p.cin, (cuuint64_t)p.wi, (cuuint64_t)p.hi, (cuuint64_t)n_capacity};
+    cuuint64_t gstr[3] = {(cuuint64_t)p.in_pitch * 2, (cuuint64_t)p.wi * p.in_pitch * 2, (cuuint64_t)p.hi * p.wi * p.in_pitch * 2};
+    cuuint32_t box[4] = {(cuuint32_t)kb, (cuuint32_t)wp, (cuuint32_t)box_rows, 1};
+    cuuint32_t es[4] = {1, 1, 1, 1};
+    CUresult r7 = g_encode_tiled(&x.map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p.in), gdim, gstr, box, es,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r7 != CUDA_SUCCESS) return tc_fail("cuTensorMapEncodeTiled(halo A, v6x) failed (%d): wp=%d rows=%d", (int)r7, wp, box_rows);
+    const cuuint64_t ktot = (cuuint64_t)taps * p.cin_pad;
+    cuuint64_t bdim[2] = {ktot, (cuuint64_t)p.cout};
+    cuuint64_t bstr[1] = {ktot * 2};
+    cuuint32_t bbox[2] = {(cuuint32_t)kb, (cuuint32_t)(x.bn / 2)};
+    cuuint32_t bes[2] = {1, 1};
+    r7 = g_encode_tiled(&x.map_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(p.w), bdim, bstr, bbox, bes,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r7 != CUDA_SUCCESS) return tc_fail("cuTensorMapEncodeTiled(weights, v6x) failed (%d)", (int)r7);
+    x.valid = true;
+    *out = x;
     return 0;
   }
   // ---- v6: halo kernel with the whole filter resident (few-channel stride-1 multi-tap layers) ----
@@ -2167,6 +2471,42 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     if (e5 != cudaSuccess) return tc_fail("conv_tc5_kernel launch: %s", cudaGetErrorString(e5));
     return 0;
   }
+  if (op.version == 7) {
+    TcV6xParams k{};
+    k.bias = p.bias;
+    k.out = reinterpret_cast<__nv_bfloat16*>(p.out);
+    if (p.n > op.m_capacity) return tc_fail("batch of %d images exceeds the planned capacity", p.n);
+    k.n_img = p.n; k.ho = p.ho; k.wo = p.wo; k.wp = op.wp; k.out_pitch = p.out_pitch;
+    k.kh = p.kh; k.kw = p.kw; k.pad_h = p.pad_h; k.pad_w = p.pad_w; k.cblocks = op.cpb;
+    k.rpt = op.rows_box; k.ptiles_per_img = op.tiles_per_img;
+    k.rows_box = op.rows_box + p.kh - 1;
+    k.a_cb_bytes = op.a_cb_bytes; k.a_stage_bytes = op.a_stage_bytes; k.a_stages = op.a_stages;
+    k.bn = op.bn; k.n_tiles = p.cout / op.bn; k.relu = p.relu; k.tmem_cols = op.tmem_cols; k.acc_stride = op.acc_stride;
+    k.n_acc = op.tmem_cols / op.acc_stride;
+    k.in_img0 = p.in_img0;
+    k.out_img0 = p.out_row0 / (p.ho * p.wo);
+    k.row_bytes = op.row_bytes;
+    k.last_kmma = (p.cin - (op.cpb - 1) * (op.row_bytes / 2) + 15) / 16;
+    k.cin_pad = p.cin_pad;
+    k.inv_wp = 1.0f / (float)op.wp;
+    k.wide_store = (p.out_pitch % 16 == 0 && reinterpret_cast<uintptr_t>(p.out) % 32 == 0) ? 1 : 0;
+    const int tiles = p.n * op.tiles_per_img;
+    const int pairs = g_num_sms / 2 / k.n_tiles;
+    const int vn = tiles < pairs ? tiles : pairs;
+    const int grid = 2 * vn * k.n_tiles;
+    bool launched = false;
+#define DML_V6X_TRY(KH_, KW_, CB_, RB_)                                                                                         \
+    if (!launched && p.kh == KH_ && p.kw == KW_ && op.cpb == CB_ && op.row_bytes == RB_) {                                        \
+      launch_pdl(conv_tc6x_kernel<KH_, KW_, CB_, RB_>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);        \
+      launched = true;                                                                                                          \
+    }
+    DML_V6X_SHAPES(DML_V6X_TRY)
+#undef DML_V6X_TRY
+    if (!launched) launch_pdl(conv_tc6x_kernel<0, 0, 0, 0>, dim3(grid), dim3(TC6_THREADS), op.smem, s, op.map_a, op.map_b, k);
+    cudaError_t e7 = cudaGetLastError();
+    if (e7 != cudaSuccess) return tc_fail("conv_tc6x_kernel launch: %s", cudaGetErrorString(e7));
+    return 0;
+  }
   if (op.version == 6) {
     TcV6Params k{};
     k.bias = p.bias;
@@ -2382,7 +2722,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     // candidates: kernel variant x N tile x k-blocks per stage (v2 / v4); duplicates of an already timed plan are skipped
     std::vector<std::array<int, 3>> seen;
     seen.push_back({plan->ops[i].version, plan->ops[i].bn, plan->ops[i].group});
-    for (int version : {4, 2, 5, 6}) {
+    for (int version : {4, 2, 5, 6, 7}) {
       for (int bn : {0, 256, 128, 64}) {
         if (version == 5 && (bn != 0 || op.cout > 128 || op.res >= 0)) continue;
         if (version == 6 && bn != 0) continue;

@@ -46,7 +46,7 @@ struct TcTune {
   int bn = 0;
   int stages = 0;
   int group = 0;    // k-blocks per pipeline stage for v2 / v4 (0 = heuristic)
-  int version = 0;  // 1 = one tile per CTA, 2 = persistent im2col, 3 = halo kernel, 4 = CTA-pair (cta_group::2) persistent, 5 = weights as A, 6 = halo kernel with the filter resident in shared memory; 0 = choose
+  int version = 0;  // 1 = one tile per CTA, 2 = persistent im2col, 3 = halo kernel, 4 = CTA-pair (cta_group::2) persistent, 5 = weights as A, 6 = halo kernel with the filter resident in shared memory, 7 = the same on CTA pairs; 0 = choose
 };
 
 bool tc_supported(const Op& op);

@@ -644,11 +644,11 @@ int dml_conv2d_bf16(int impl, const void* d_in, const void* d_w, const float* d_
     if (dml::launch_stem_tc(p, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "stem conv launch failed");
     return 0;
   }
-  if (impl < 1 || impl > 7) return fail(DML_EINVAL, "impl must be 0 (CUDA cores), 1 (tcgen05, tile per CTA), 2 (tcgen05, persistent im2col), 3 (C=3 stem), 4 (tcgen05 halo kernel), 5 (CTA pairs), 6 (weights as A) or 7 (halo kernel, resident filter)");
+  if (impl < 1 || impl > 8) return fail(DML_EINVAL, "impl must be 0 (CUDA cores), 1 (tcgen05, tile per CTA), 2 (tcgen05, persistent im2col), 3 (C=3 stem), 4 (tcgen05 halo kernel), 5 (CTA pairs), 6 (weights as A), 7 (halo kernel, resident filter) or 8 (the same on CTA pairs)");
   if (dml::tc_init() != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
   dml::TcOpPlan plan;
   dml::TcTune tune;
-  tune.bn = tile_n; tune.stages = stages & 0xff; tune.group = (stages >> 8) & 0xff; tune.version = impl == 4 ? 3 : (impl == 5 ? 4 : (impl == 6 ? 5 : (impl == 7 ? 6 : impl)));  // 5 = CTA-pair kernel, 6 = weights-as-A kernel, 7 = resident-filter halo kernel
+  tune.bn = tile_n; tune.stages = stages & 0xff; tune.group = (stages >> 8) & 0xff; tune.version = impl == 4 ? 3 : (impl == 5 ? 4 : (impl == 6 ? 5 : (impl == 7 ? 6 : (impl == 8 ? 7 : impl))));  // 5 = CTA-pair kernel, 6 = weights-as-A kernel, 7 = resident-filter halo kernel, 8 = the same on CTA pairs
   if (dml::tc_plan_one(&plan, p, n, tune) != 0) return fail(DML_EINVAL, "%s", dml::tc_last_error());
   if (dml::launch_conv_tc_plan(plan, p, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
   return 0;

@@ -158,7 +158,10 @@ int dml_launch_count(dml_engine* e, int64_t* launches);
  * over explicit device buffers: bf16 NHWC activations (channel pitches in
  * elements), packed bf16 weights [cout][kh*kw][cin_pad], fp32 bias.
  * impl 0 = CUDA-core kernel, 1 = tcgen05 one-tile-per-CTA kernel, 2 = persistent
- * tcgen05 kernel (the production one); tile_n / stages: 0 = default;
+ * tcgen05 kernel, 3 = C=3 stride-2 stem, 4 = halo kernel with streamed weights,
+ * 5 = persistent kernel on CTA pairs, 6 = weights as the A operand, 7 = halo kernel
+ * with the filter resident in shared memory, 8 = the same on CTA pairs (the engine
+ * picks per layer among 2, 5, 6, 7, 8); tile_n / stages: 0 = default;
  * bits 8..15 of `stages` = 64-channel k-blocks per pipeline stage for impl 2 / 5 (0 = default).
  * The unit-test and tuning hook for the convolution kernels. */
 int dml_conv2d_bf16(int impl, const void* d_in, const void* d_w, const float* d_bias, const void* d_res, void* d_out,

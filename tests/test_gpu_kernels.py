@@ -298,6 +298,35 @@ def test_conv_tcgen05_resident_filter_halo(shape):
     assert torch.equal(out, _run_conv(2, case))   # same bits as the im2col kernel
 
 
+PAIR_HALO_CASES = [
+    (3, 28, 28, 128, 128, 3, 3, 1, 1, 1, True, False, 0, 0),       # ResNet50 conv3 3x3
+    (5, 28, 28, 128, 128, 3, 3, 1, 1, 1, False, False, 0, 0),      # odd image count: tiles wrap over the clusters
+    (2, 35, 35, 48, 64, 5, 5, 1, 2, 2, True, False, 0, 32),        # InceptionV3 5x5, ragged Cin, concat slice
+    (2, 35, 35, 96, 96, 3, 3, 1, 1, 1, True, False, 0, 160),       # 3x3 96 -> 96 (two channel blocks, second one ragged)
+    (2, 17, 17, 128, 128, 1, 7, 1, 0, 3, True, False, 0, 0),       # 1x7
+    (2, 17, 17, 160, 192, 7, 1, 1, 3, 0, True, False, 0, 576),     # 7x1, three channel blocks, Cout 192
+    (300, 14, 14, 64, 64, 3, 3, 1, 1, 1, True, False, 0, 0),       # many tiles per cluster: rings and accumulators wrap
+    (2, 56, 56, 64, 64, 3, 3, 1, 1, 1, True, False, 0, 0),         # two rows per tile
+    (3, 9, 9, 32, 32, 3, 3, 1, 0, 0, False, False, 0, 0),          # 64-byte rows, valid conv, generic loop
+]
+
+
+@pytest.mark.parametrize("shape", PAIR_HALO_CASES, ids=lambda s: "x".join(map(str, s[:10])))
+def test_conv_tcgen05_pair_resident_filter_halo(shape):
+    """impl 8: resident-filter halo kernel on CTA pairs (row-aligned tiles)."""
+    import torch
+    rng = np.random.default_rng(hash(shape) % 2**32)
+    case = _conv_case(rng, *shape)
+    out = _run_conv(8, case)
+    cout = shape[4]
+    ref = case["ref"]
+    got = out[..., :cout].float()
+    assert (got - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
+    if shape[13]:
+        assert (out[..., cout:].float() == 7.0).all()
+    assert torch.equal(out, _run_conv(2, case))   # same bits as the im2col kernel
+
+
 def test_conv_tcgen05_variants_are_bit_identical():
     """Tile shape and kernel variant must not change a single bit (the engine may pick any of them)."""
     import torch
