@@ -327,6 +327,7 @@ struct TcV2Params {
   int last_kmma;    // K=16 steps that carry real channels in the last 64-channel block of a tap (1..4)
   int group;        // 64-channel k-blocks per pipeline stage: one barrier round trip per `group` x 4 MMAs
   int prof;         // DML_TC_PROF: per-role cycle counters into g_tc2_prof (v2 only)
+  int M_cap;        // rows of the output / residual tensors (direct residual loads stop there)
 };
 
 __device__ long long g_tc2_prof[160 * 8];
@@ -1262,12 +1263,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
   const uint32_t sB = sA + (uint32_t)(stages * G) * A_STAGE_BYTES;
   const uint32_t sO = sB + (uint32_t)(stages * G) * b_half_bytes;
   const uint32_t res_tile_bytes = p.has_res ? (uint32_t)BLOCK_M * (uint32_t)p.bn * 2u : 0u;
+  const uint32_t res_bufs = p.has_res == 2 ? 1u : 2u;  // has_res == 2: ONE tile buffer whose column chunks are released one by one
   const uint32_t sR = sO + OUT_STAGING_BYTES;
-  const uint32_t bars = sR + 2u * res_tile_bytes;
+  const uint32_t bars = sR + res_bufs * res_tile_bytes;
   const uint32_t full0 = bars, empty0 = bars + 8u * stages;
   const uint32_t tfull0 = bars + 16u * stages, tempty0 = tfull0 + 16u;
-  const uint32_t rfull0 = tempty0 + 16u, rempty0 = rfull0 + 16u;
-  const uint32_t tmem_slot = rempty0 + 16u;
+  const uint32_t rfull0 = tempty0 + 16u, rempty0 = rfull0 + 32u;  // 2 tile buffers (mode 1) or up to 4 chunk slots (mode 2)
+  const uint32_t tmem_slot = rempty0 + 32u;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -1286,8 +1288,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull0 + 8u * i, 1);
       mbar_init(tempty0 + 8u * i, 16);  // leader: 8 epilogue warps of each CTA
+    }
+    for (int i = 0; i < 4; ++i) {
       mbar_init(rfull0 + 8u * i, 1);
-      mbar_init(rempty0 + 8u * i, 8);
+      mbar_init(rempty0 + 8u * i, p.has_res == 2 ? 4 : 8);  // chunk slot: the 4 warps that read it; tile buffer: all 8
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -1315,7 +1319,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
       const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
       const int m0 = mt * 2 * BLOCK_M + (int)rank * BLOCK_M, n0 = nt * p.bn;
-      if (p.has_res) {
+      if (p.has_res == 1) {
         const uint32_t rb = lt & 1u, rph = (lt >> 1) & 1u;
         mbar_wait_spin(rempty0 + 8u * rb, rph ^ 1u);
         if (elect_one()) {
@@ -1354,6 +1358,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
             cb = 0;
             if (++sx == p.kw) { sx = 0; ++r; }
           }
+        }
+      }
+      if (p.has_res == 2) {
+        // single residual buffer: chunk slot c is refilled as soon as the previous tile's epilogue has read it.  Issued
+        // after this tile's operand loads: the wait below depends on epilogue(t-1), which MMA(t+1) needs anyway.
+        const uint32_t rph = lt & 1u;
+        for (int c = 0, ci = 0; c < p.bn; c += p.cw, ++ci) {
+          mbar_wait_spin(rempty0 + 8u * ci, rph ^ 1u);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(rfull0 + 8u * ci, chunk_bytes);
+            tma_load_2d(sR + (uint32_t)ci * chunk_bytes, &map_r, rfull0 + 8u * ci, n0 + c, p.out_row0 + m0);
+          }
+          __syncwarp();
         }
       }
     }
@@ -1437,17 +1454,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
       const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
       const int m0 = mt * 2 * BLOCK_M + (int)rank * BLOCK_M, n0 = nt * p.bn;
       const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
-      if (p.has_res) mbar_wait(rfull0 + 8u * a, aph);
+      if (p.has_res == 1) mbar_wait(rfull0 + 8u * a, aph);
       mbar_wait(tfull0 + 8u * a, aph);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + a * (uint32_t)p.acc_stride;
-      const uint32_t r_row = sR + a * res_tile_bytes + (uint32_t)(q * 32 + lane) * row_bytes;
+      const uint32_t r_row = sR + (p.has_res == 2 ? 0u : a * res_tile_bytes) + (uint32_t)(q * 32 + lane) * row_bytes;
       int ci = half;
       for (int c0 = half * cw; c0 < p.bn; c0 += 2 * cw, ++nstore, ci += 2) {
         const uint32_t sbuf = my_out + (nstore & 1u) * OUT_BUF_BYTES;
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
         __syncwarp();
         const uint32_t rowaddr = sbuf + (uint32_t)lane * row_bytes;
+        if (p.has_res == 2) mbar_wait(rfull0 + 8u * (uint32_t)ci, lt & 1u);  // this chunk of the residual tile has landed
         for (int g = 0; g < cw; g += 32) {
           uint32_t v[2][16];
           const bool two = g + 16 < cw;
@@ -1507,13 +1525,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
         if (lane == 0) {
           tma_store_2d(&map_o, sbuf, n0 + c0, p.out_row0 + m0 + q * 32);
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          if (p.has_res == 2) mbar_arrive(rempty0 + 8u * (uint32_t)ci);  // this warp is done with its rows of chunk ci
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
         mbar_arrive_leader(tempty0 + 8u * a);  // the leader's MMA warp waits for both CTAs
-        if (p.has_res) mbar_arrive(rempty0 + 8u * a);
+        if (p.has_res == 1) mbar_arrive(rempty0 + 8u * a);
       }
     }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
@@ -2326,9 +2345,15 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
   const long long M_cap = (long long)n_capacity * p.ho * p.wo;
   const long long m_tiles_cap = pair ? (M_cap + 2 * BLOCK_M - 1) / (2 * BLOCK_M) : (M_cap + BLOCK_M - 1) / BLOCK_M;
   op.has_res = op.version != 1 && p.res != nullptr;
+  // residual in ONE tile buffer whose column chunks are handed back one by one (pair kernel) instead of two whole tile
+  // buffers: frees 128 x bn x 2 bytes of shared memory, so the N tile can stay at 256 with a 3-stage operand ring (the A
+  // tile is then re-read half as often; these layers are bound by the bytes an SM can ingest)
+  op.res_direct = op.has_res && pair && (tune.res_direct == 2 || (tune.res_direct == 0 && !getenv("DML_NO_RES_CHUNKS")));
+  const int res_bufs = op.has_res ? (op.res_direct ? 1 : 2) : 0;
+  const bool res_smem = op.has_res && !op.res_direct;
   op.bn = op.version == 1 ? pick_bn(p.cout, tune.bn) : pick_bn_v2(p.cout, pair ? 2 * m_tiles_cap : m_tiles_cap, tune.bn);
   // two residual tiles of 128 x bn bf16 live in shared memory: keep them at 64 KiB
-  if (op.has_res && tune.bn == 0 && op.bn > 128 && !pair) op.bn = pick_bn(p.cout, 0);
+  if (res_smem && tune.bn == 0 && op.bn > 128 && !pair) op.bn = pick_bn(p.cout, 0);
   if (op.bn == 0) return tc_fail("no N tile for cout = %d (override %d)", p.cout, tune.bn);
   if (p.cin_pad % BLOCK_K) return tc_fail("cin_pad = %d is not a multiple of %d", p.cin_pad, BLOCK_K);
   op.cpb = p.cin_pad / BLOCK_K;
@@ -2344,7 +2369,7 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
     op.tmem_cols = 32;
     while (op.tmem_cols < op.bn) op.tmem_cols *= 2;
   } else {
-    int fixed = 1024 /*alignment slack*/ + OUT_STAGING_BYTES + 256 /*barriers*/ + (op.has_res ? 2 * BLOCK_M * op.bn * 2 : 0);
+    int fixed = 1024 /*alignment slack*/ + OUT_STAGING_BYTES + 256 /*barriers*/ + res_bufs * BLOCK_M * op.bn * 2;
     int sb = stage_bytes;
     // the two residual tiles may not leave room for two stages at the widest N tile: narrow it (heuristic choice only)
     while (tune.bn == 0 && (SMEM_LIMIT - fixed) / sb < 2 && op.bn > 64) {
@@ -2353,7 +2378,7 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
         if (p.cout % c == 0) { nb = c; break; }
       if (!nb) break;
       op.bn = nb;
-      fixed = 1024 + OUT_STAGING_BYTES + 256 + (op.has_res ? 2 * BLOCK_M * op.bn * 2 : 0);
+      fixed = 1024 + OUT_STAGING_BYTES + 256 + res_bufs * BLOCK_M * op.bn * 2;
       sb = A_STAGE_BYTES + (pair ? op.bn * 64 : op.bn * 128);
     }
     // k-blocks per stage: the MMA warp pays one barrier wait + one commit per STAGE, so narrow N tiles
@@ -2374,6 +2399,7 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
     while (op.acc_stride < op.bn) op.acc_stride *= 2;
     op.tmem_cols = 2 * op.acc_stride;
     op.cw = op.bn % 64 == 0 ? 64 : (op.bn % 32 == 0 ? 32 : 16);
+    if (op.res_direct && op.bn / op.cw > 4) return tc_fail("chunked residual buffer needs at most 4 column chunks (bn %d, cw %d)", op.bn, op.cw);
     op.m_capacity = (int)M_cap;
     if (!p.out) return tc_fail("output pointer needed to plan the persistent kernel");
     cuuint64_t odim[2] = {(cuuint64_t)p.cout, (cuuint64_t)M_cap};
@@ -2584,7 +2610,8 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.bias = p.bias;
     k.res = reinterpret_cast<const __nv_bfloat16*>(p.res);
     k.M = p.n * p.ho * p.wo;
-    k.has_res = op.has_res ? 1 : 0;
+    k.has_res = op.has_res ? (op.res_direct ? 2 : 1) : 0;
+    k.M_cap = op.m_capacity;
     k.in_img0 = p.in_img0;
     k.a_tiled = op.a_tiled ? 1 : 0;
     k.last_kmma = (p.cin - (op.cpb - 1) * BLOCK_K + 15) / 16;
@@ -2742,6 +2769,18 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
           if (tune_log) fprintf(stderr, "[tune]   %s v%d bn %d group %d stages %d: %.4f ms\n", op.name.c_str(), cand.version, cand.bn, cand.group, cand.stages, ms);
           if (ms < best * 0.98f) { best = ms; plan->ops[i] = cand; }
         }
+      }
+    }
+    if (op.res >= 0) {  // residual layers: also with two whole residual tile buffers instead of the chunked single one
+      for (int bn : {0, 256, 128}) {
+        if (bn && (op.cout % bn != 0 || bn > op.cout)) continue;
+        TcTune t;
+        t.version = 4; t.bn = bn; t.res_direct = 1;
+        TcOpPlan cand;
+        if (tc_plan_one(&cand, p, micro_batch, t) != 0) continue;
+        float ms = time_plan(cand, p, ev0, ev1);
+        if (tune_log) fprintf(stderr, "[tune]   %s v%d bn %d group %d stages %d (two residual tile buffers): %.4f ms\n", op.name.c_str(), cand.version, cand.bn, cand.group, cand.stages, ms);
+        if (ms < best * 0.98f) { best = ms; plan->ops[i] = cand; }
       }
     }
     if (tune_log)

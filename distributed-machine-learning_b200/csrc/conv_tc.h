@@ -29,6 +29,7 @@ struct TcOpPlan {
   int m_capacity = 0;  // rows the output map covers
   alignas(64) CUtensorMap map_r;  // residual view, same geometry as the output
   bool has_res = false;
+  bool res_direct = false;  // v4: ONE residual tile buffer with per-chunk hand-back instead of two tile buffers
   bool a_tiled = false;  // A fetched with a tiled 2D map (1x1 stride-1 convs)
   // v3 (halo kernel)
   int wp = 0, rows_box = 0, tiles_per_img = 0, q_valid = 0, a_stage_bytes = 0, a_stages = 0, b_stages = 0;
@@ -46,6 +47,7 @@ struct TcTune {
   int bn = 0;
   int stages = 0;
   int group = 0;    // k-blocks per pipeline stage for v2 / v4 (0 = heuristic)
+  int res_direct = 0;  // v4 residual staging: 0 = heuristic, 1 = two tile buffers, 2 = one buffer, chunks handed back one by one
   int version = 0;  // 1 = one tile per CTA, 2 = persistent im2col, 3 = halo kernel, 4 = CTA-pair (cta_group::2) persistent, 5 = weights as A, 6 = halo kernel with the filter resident in shared memory, 7 = the same on CTA pairs; 0 = choose
 };
 

@@ -339,7 +339,8 @@ def test_conv_tcgen05_variants_are_bit_identical():
         outs = [_run_conv(2, case, 0, 0), _run_conv(2, case, 64, 2), _run_conv(2, case, big, 0), _run_conv(5, case, 0, 0),
                 _run_conv(5, case, 64, 3), _run_conv(1, case, 0, 0), _run_conv(2, case, 64, g(1)), _run_conv(2, case, 64, g(4)),
                 _run_conv(2, case, 32, g(5, 2)), _run_conv(5, case, 64, g(1)), _run_conv(5, case, 64, g(3)),
-                _run_conv(5, case, big, g(2, 2)), _run_conv(5, case, 32, g(7))]
+                _run_conv(5, case, big, g(2, 2)), _run_conv(5, case, 32, g(7)),
+                _run_conv(5, case, 0, 1 << 16), _run_conv(5, case, 0, 2 << 16), _run_conv(5, case, 64, (2 << 16) | g(2))]  # residual paths
         for o in outs[1:]:
             assert torch.equal(o, outs[0])
 

@@ -27,15 +27,17 @@ def main():
     wp[:, :, :cin] = torch.from_numpy((rng.standard_normal((cout, k * k, cin)) / np.sqrt(k * k * cin)).astype(np.float32)).to(dev).bfloat16()
     bias = torch.zeros(cout, dtype=torch.float32, device=dev)
     out = torch.empty((n, ho, ho, cout), dtype=torch.bfloat16, device=dev)
-    geom = (n, hi, wi, cin, cin, cout, cout, 0, k, k, stride, pad, pad, cin_pad, 1)
+    with_res = os.environ.get("DML_PROF_RES") is not None   # add a residual input (the 1x1 expand layers of ResNet50)
+    res = torch.from_numpy(rng.standard_normal((n, ho, ho, cout)).astype(np.float32)).to(dev).bfloat16() if with_res else None
+    geom = (n, hi, wi, cin, cin, cout, cout, cout if with_res else 0, k, k, stride, pad, pad, cin_pad, 1)
     flop = 2.0 * n * ho * ho * cout * k * k * cin
     first = None
     for spec in sys.argv[9:]:
         impl, tile_n, stages, group = [int(v) for v in spec.split(":")]
 
         def run():
-            lib.check(lib.lib().dml_conv2d_bf16(impl, x.data_ptr(), wp.data_ptr(), bias.data_ptr(), None, out.data_ptr(), *geom,
-                                                tile_n, stages | (group << 8), None))
+            lib.check(lib.lib().dml_conv2d_bf16(impl, x.data_ptr(), wp.data_ptr(), bias.data_ptr(), res.data_ptr() if res is not None else None, out.data_ptr(), *geom,
+                                                tile_n, stages | (group << 8) | (int(os.environ.get("DML_PROF_RESMODE", "0")) << 16), None))
         for _ in range(3):
             run()
         torch.cuda.synchronize()
