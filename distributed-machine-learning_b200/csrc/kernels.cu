@@ -285,15 +285,17 @@ __global__ void __launch_bounds__(256) pool_kernel(PoolParams p) {
 __global__ void __launch_bounds__(256) maxpool3_bf16_kernel(PoolParams p) {
   pdl_launch_dependents();
   pdl_wait();
-  const int cg = p.c >> 3;
-  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (int64_t)p.n * p.ho * p.wo * cg) return;
-  const int g = (int)(idx % cg);
-  int64_t pix = idx / cg;
-  const int wo = (int)(pix % p.wo);
-  int64_t t = pix / p.wo;
-  const int ho = (int)(t % p.ho);
-  const int n = (int)(t / p.ho);
+  // 32-bit index arithmetic (the launcher checks the thread count fits): 64-bit divisions were most of this kernel's
+  // instructions (ncu: 67 % issue activity at 62 % of DRAM throughput)
+  const uint32_t cg = (uint32_t)p.c >> 3;
+  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (uint32_t)p.n * (uint32_t)p.ho * (uint32_t)p.wo * cg) return;
+  const uint32_t pix = idx / cg;
+  const int g = (int)(idx - pix * cg);
+  const uint32_t t = pix / (uint32_t)p.wo;
+  const int wo = (int)(pix - t * (uint32_t)p.wo);
+  const int n = (int)(t / (uint32_t)p.ho);
+  const int ho = (int)(t - (uint32_t)n * (uint32_t)p.ho);
   const __nv_bfloat16* in = reinterpret_cast<const __nv_bfloat16*>(p.in) + (int64_t)n * p.hi * p.wi * p.in_pitch + g * 8;
   const int h0 = ho * p.stride - p.pad, w0 = wo * p.stride - p.pad;
   uint4 raw[9];
@@ -304,7 +306,7 @@ __global__ void __launch_bounds__(256) maxpool3_bf16_kernel(PoolParams p) {
       const int hi = h0 + r, wi = w0 + s;
       raw[r * 3 + s] = make_uint4(0, 0, 0, 0);  // bf16 zeros = what ZeroPadding2D contributes
       if (hi >= 0 && hi < p.hi && wi >= 0 && wi < p.wi)
-        raw[r * 3 + s] = *reinterpret_cast<const uint4*>(in + ((int64_t)hi * p.wi + wi) * p.in_pitch);
+        raw[r * 3 + s] = *reinterpret_cast<const uint4*>(in + (hi * p.wi + wi) * p.in_pitch);  // one image < 2^31 elements
     }
   // pad == 0: every tap is in bounds, so starting from tap 0 is exact; pad > 0: zeros take part like any tap
   __nv_bfloat162 m[4];
@@ -334,12 +336,15 @@ __global__ void __launch_bounds__(256) avgpool3_kernel(PoolParams p) {
   constexpr int V = Vec16<T>::N;
   const int cg = p.c / V;
   const int segs = (p.hi + AVG_ROWS - 1) / AVG_ROWS;
-  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (int64_t)p.n * segs * p.wi * cg) return;
-  const int g = (int)(idx % cg);
-  const int wo = (int)((idx / cg) % p.wi);
-  const int seg = (int)((idx / ((int64_t)cg * p.wi)) % segs);
-  const int n = (int)(idx / ((int64_t)cg * p.wi * segs));
+  // 32-bit index arithmetic (the launcher checks the thread count fits)
+  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (uint32_t)p.n * (uint32_t)segs * (uint32_t)p.wi * (uint32_t)cg) return;
+  const uint32_t q1 = idx / (uint32_t)cg;
+  const int g = (int)(idx - q1 * (uint32_t)cg);
+  const uint32_t q2 = q1 / (uint32_t)p.wi;
+  const int wo = (int)(q1 - q2 * (uint32_t)p.wi);
+  const int n = (int)(q2 / (uint32_t)segs);
+  const int seg = (int)(q2 - (uint32_t)n * (uint32_t)segs);
   const T* in = reinterpret_cast<const T*>(p.in) + (int64_t)n * p.hi * p.wi * p.in_pitch + g * V;
   T* out = reinterpret_cast<T*>(p.out) + (int64_t)n * p.hi * p.wi * p.out_pitch + g * V;
   const int w0 = wo > 0 ? wo - 1 : 0, w1 = wo < p.wi - 1 ? wo + 1 : p.wi - 1;
@@ -354,7 +359,7 @@ __global__ void __launch_bounds__(256) avgpool3_kernel(PoolParams p) {
     for (int j = 0; j < 3; ++j) {
       const int wi = w0 + j;
       raw[j] = make_uint4(0, 0, 0, 0);
-      if (wi <= w1) raw[j] = *reinterpret_cast<const uint4*>(in + ((int64_t)r * p.wi + wi) * p.in_pitch);
+      if (wi <= w1) raw[j] = *reinterpret_cast<const uint4*>(in + (r * p.wi + wi) * p.in_pitch);  // one image < 2^31 elements
     }
 #pragma unroll
     for (int i = 0; i < V; ++i) h[i] = 0.f;
@@ -378,7 +383,7 @@ __global__ void __launch_bounds__(256) avgpool3_kernel(PoolParams p) {
       float sum = h1[i] + (r > 0 ? h0[i] : 0.f) + (has_next ? h2[i] : 0.f);
       o[i] = from_f<T>(sum * inv);
     }
-    *reinterpret_cast<uint4*>(out + ((int64_t)r * p.wi + wo) * p.out_pitch) = *reinterpret_cast<uint4*>(o);
+    *reinterpret_cast<uint4*>(out + (r * p.wi + wo) * p.out_pitch) = *reinterpret_cast<uint4*>(o);
 #pragma unroll
     for (int i = 0; i < V; ++i) { h0[i] = h1[i]; h1[i] = h2[i]; }
   }
@@ -565,7 +570,7 @@ static void launch_pool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
   else pool_kernel<__nv_bfloat16, AVG><<<blocks, 256, 0, s>>>(p);
 }
 void launch_maxpool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
-  if (!fp32_act && p.k == 3) {
+  if (!fp32_act && p.k == 3 && (int64_t)p.n * p.ho * p.wo * (p.c / 8) < (1ll << 31) && (int64_t)p.hi * p.wi * p.in_pitch < (1ll << 31)) {
     int64_t total = (int64_t)p.n * p.ho * p.wo * (p.c / 8);
     launch_pdl(maxpool3_bf16_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, s, p);
     return;
@@ -573,7 +578,9 @@ void launch_maxpool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
   launch_pool<false>(p, fp32_act, s);
 }
 void launch_avgpool(const PoolParams& p, bool fp32_act, cudaStream_t s) {
-  if (p.k == 3 && p.stride == 1 && p.pad == 1 && p.ho == p.hi && p.wo == p.wi) {
+  if (p.k == 3 && p.stride == 1 && p.pad == 1 && p.ho == p.hi && p.wo == p.wi &&
+      (int64_t)p.n * ((p.hi + AVG_ROWS - 1) / AVG_ROWS) * p.wi * (p.c / (fp32_act ? 4 : 8)) < (1ll << 31) &&
+      (int64_t)p.hi * p.wi * (p.in_pitch > p.out_pitch ? p.in_pitch : p.out_pitch) < (1ll << 31)) {
     int V = fp32_act ? 4 : 8;
     int64_t total = (int64_t)p.n * ((p.hi + AVG_ROWS - 1) / AVG_ROWS) * p.wi * (p.c / V);
     unsigned blocks = (unsigned)((total + 255) / 256);
