@@ -361,26 +361,32 @@ __global__ void __launch_bounds__(256) avgpool3_kernel(PoolParams p) {
       raw[j] = make_uint4(0, 0, 0, 0);
       if (wi <= w1) raw[j] = *reinterpret_cast<const uint4*>(in + (r * p.wi + wi) * p.in_pitch);  // one image < 2^31 elements
     }
+    const T* va = reinterpret_cast<const T*>(&raw[0]);
+    const T* vb = reinterpret_cast<const T*>(&raw[1]);
+    const T* vc = reinterpret_cast<const T*>(&raw[2]);
 #pragma unroll
-    for (int i = 0; i < V; ++i) h[i] = 0.f;
-#pragma unroll
-    for (int j = 0; j < 3; ++j) {
-      const T* v = reinterpret_cast<const T*>(&raw[j]);
-#pragma unroll
-      for (int i = 0; i < V; ++i) h[i] += to_f(v[i]);  // same left-to-right order as before: w0, w0+1, w0+2
-    }
+    for (int i = 0; i < V; ++i) h[i] = (to_f(va[i]) + to_f(vb[i])) + to_f(vc[i]);  // left to right: w0, w0+1, w0+2 (an absent column adds an exact 0)
   };
   if (r_begin > 0) hsum(r_begin - 1, h0);
   hsum(r_begin, h1);
-  for (int r = r_begin; r < r_end; ++r) {
+#pragma unroll
+  for (int k = 0; k < AVG_ROWS; ++k) {
+    const int r = r_begin + k;
+    if (r >= r_end) break;
     const bool has_next = r + 1 < p.hi;
-    if (has_next) hsum(r + 1, h2);
+    if (has_next) {
+      hsum(r + 1, h2);
+    } else {
+#pragma unroll
+      for (int i = 0; i < V; ++i) h2[i] = 0.f;
+    }
     const float nrows = (float)((r > 0) + 1 + has_next);
     const float inv = 1.f / (nrows * ncols);
     T o[V];
 #pragma unroll
     for (int i = 0; i < V; ++i) {
-      float sum = h1[i] + (r > 0 ? h0[i] : 0.f) + (has_next ? h2[i] : 0.f);
+      // h0 is all zeros above the first row and h2 below the last one: adding them is exact
+      float sum = h1[i] + h0[i] + h2[i];
       o[i] = from_f<T>(sum * inv);
     }
     *reinterpret_cast<uint4*>(out + (r * p.wi + wo) * p.out_pitch) = *reinterpret_cast<uint4*>(o);
