@@ -243,6 +243,10 @@ PAIR_CASES = [
     ((9, 35, 35, 64, 96, 3, 3, 1, 1, 1, True, False, 0, 160), 0, 0),     # bn 96, concat slice
     ((2, 17, 17, 160, 192, 7, 1, 1, 3, 0, True, False, 0, 576), 0, 0),
     ((1, 5, 5, 64, 32, 1, 1, 1, 0, 0, False, False, 0, 0), 0, 0),        # one partial tile: peer CTA has no rows
+    ((2, 73, 73, 80, 192, 3, 3, 1, 0, 0, True, False, 0, 0), 0, 0),      # Cin 80: ragged last channel block
+    ((2, 73, 73, 80, 192, 3, 3, 1, 0, 0, True, False, 0, 0), 64, 2 | (3 << 8)),  # the same, 3 k-blocks per stage
+    ((3, 35, 35, 288, 64, 1, 1, 1, 0, 0, True, False, 0, 224), 0, 0),    # Cin 288, 1x1 tiled A into a concat slice
+    ((2, 17, 17, 96, 96, 3, 3, 2, 0, 0, True, False, 32, 0), 0, 0),      # Cin 96 stride 2, input is a channel slice
 ]
 
 
