@@ -63,7 +63,7 @@ def get_engine(model_name: str, device: int | None = None) -> Engine:
 def _pool():
     global _decode_pool
     if _decode_pool is None:
-        _decode_pool = ThreadPoolExecutor(max_workers=min(16, os.cpu_count() or 4))
+        _decode_pool = ThreadPoolExecutor(max_workers=min(32, os.cpu_count() or 4))  # Pillow releases the GIL while it decodes
     return _decode_pool
 
 
