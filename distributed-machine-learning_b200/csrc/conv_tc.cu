@@ -327,7 +327,9 @@ struct TcV2Params {
   int last_kmma;    // K=16 steps that carry real channels in the last 64-channel block of a tap (1..4)
   int group;        // 64-channel k-blocks per pipeline stage: one barrier round trip per `group` x 4 MMAs
   int prof;         // DML_TC_PROF: per-role cycle counters into g_tc2_prof (v2 only)
-  int M_cap;        // rows of the output / residual tensors (direct residual loads stop there)
+  int M_cap;        // rows of the output / residual tensors
+  int kb1;          // k-blocks of the first GEMM source; [kb1, num_kb) come from the second one (pair kernel)
+  int stride2, a2_tiled, in2_row0;
 };
 
 __device__ long long g_tc2_prof[160 * 8];
@@ -1252,7 +1254,7 @@ __device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
     conv_tc2x_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                      const __grid_constant__ CUtensorMap map_o, const __grid_constant__ CUtensorMap map_r,
-                     const TcV2Params p) {
+                     const __grid_constant__ CUtensorMap map_a2, const TcV2Params p) {
   pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -1281,6 +1283,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_o) : "memory");
+    if (p.kb1 < p.num_kb) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a2) : "memory");
     for (int i = 0; i < stages; ++i) {
       mbar_init(full0 + 8u * i, 1);   // leader: its own arrive.expect_tx covers the bytes of both CTAs
       mbar_init(empty0 + 8u * i, 1);  // one multicast commit per stage
@@ -1347,7 +1350,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
         for (int g = 0; g < cnt; ++g) {
           {
             const uint32_t sub = s * (uint32_t)G + (uint32_t)g;
-            if (p.a_tiled)
+            const int j = j0 + g;
+            if (j >= p.kb1) {
+              // second GEMM source (the folded projection shortcut): 1x1 convolution of stride stride2 over another tensor
+              if (p.a2_tiled)
+                tma2_load_2d_elect(sA + sub * A_STAGE_BYTES, &map_a2, full0 + 8u * s, (j - p.kb1) * BLOCK_K, p.in2_row0 + m0);
+              else
+                tma2_load_im2col_4d_elect(sA + sub * A_STAGE_BYTES, &map_a2, full0 + 8u * s, (j - p.kb1) * BLOCK_K, ow * p.stride2,
+                                          oh * p.stride2, img + p.in_img0, (uint16_t)0, (uint16_t)0);
+            } else if (p.a_tiled)
               tma2_load_2d_elect(sA + sub * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, p.in_row0 + m0);
             else
               tma2_load_im2col_4d_elect(sA + sub * A_STAGE_BYTES, &map_a, full0 + 8u * s, cb * BLOCK_K, w_base, h_base,
@@ -2341,6 +2352,12 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
   op.version = tune.version == 1 ? 1 : (tune.version == 4 ? 4 : 2);
   // default: CTA pairs (3-8 % faster on almost every layer) when there are enough 256-row tiles
   if (tune.version == 0 && !getenv("DML_NO_PAIR") && (long long)n_capacity * p.ho * p.wo >= 2 * BLOCK_M) op.version = 4;
+  if (p.in2) {  // second GEMM source: pair kernel only
+    if (tune.version != 0 && tune.version != 4) return tc_fail("only the CTA-pair kernel reads a second GEMM source");
+    if (p.kh != 1 || p.kw != 1 || p.cin % BLOCK_K || p.cin2 % BLOCK_K || p.cin2_pad != p.cin2 || p.res)
+      return tc_fail("second GEMM source needs a 1x1 convolution, channel counts that are multiples of 64 and no residual");
+    op.version = 4;
+  }
   const bool pair = op.version == 4;  // CTA pairs: 256-row tiles, each CTA stages half of the weight tile
   const long long M_cap = (long long)n_capacity * p.ho * p.wo;
   const long long m_tiles_cap = pair ? (M_cap + 2 * BLOCK_M - 1) / (2 * BLOCK_M) : (M_cap + BLOCK_M - 1) / BLOCK_M;
@@ -2357,7 +2374,7 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
   if (op.bn == 0) return tc_fail("no N tile for cout = %d (override %d)", p.cout, tune.bn);
   if (p.cin_pad % BLOCK_K) return tc_fail("cin_pad = %d is not a multiple of %d", p.cin_pad, BLOCK_K);
   op.cpb = p.cin_pad / BLOCK_K;
-  const int num_kb = p.kh * p.kw * op.cpb;
+  const int num_kb = p.kh * p.kw * op.cpb + p.cin2_pad / BLOCK_K;
   const int stage_bytes = A_STAGE_BYTES + (pair ? op.bn * 64 : op.bn * 128);
   if (op.version == 1) {
     int target = op.bn <= 64 ? 3 : (op.bn <= 128 ? 3 : 4);
@@ -2455,8 +2472,8 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
   if (g_driver_version <= 13010 && (size_t)n_capacity * p.hi * p.wi * p.in_pitch * 2 < 131072)
     reinterpret_cast<uint64_t*>(&op.map_a)[1] &= ~(1ull << 21);
 
-  // B: packed weights [cout][taps*cin_pad], K contiguous.
-  const cuuint64_t ktot = (cuuint64_t)p.kh * p.kw * p.cin_pad;
+  // B: packed weights [cout][taps*cin_pad (+ cin2_pad)], K contiguous.
+  const cuuint64_t ktot = (cuuint64_t)p.kh * p.kw * p.cin_pad + (cuuint64_t)p.cin2_pad;
   cuuint64_t bdim[2] = {ktot, (cuuint64_t)p.cout};
   cuuint64_t bstr[1] = {ktot * 2};
   cuuint32_t bbox[2] = {BLOCK_K, (cuuint32_t)(pair ? op.bn / 2 : op.bn)};
@@ -2466,6 +2483,35 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return tc_fail("cuTensorMapEncodeTiled(weights) failed (%d): K=%llu cout=%d bn=%d", (int)r,
                                         (unsigned long long)ktot, p.cout, op.bn);
+  op.map_a2 = op.map_a;
+  op.a2_tiled = false;
+  if (p.in2) {
+    // second source: 1x1 convolution of stride stride2, no padding, over (C2, W2, H2, N)
+    if ((p.hi2 - 1) / p.stride2 + 1 != p.ho || (p.wi2 - 1) / p.stride2 + 1 != p.wo)
+      return tc_fail("second GEMM source %dx%d at stride %d does not produce %dx%d", p.hi2, p.wi2, p.stride2, p.ho, p.wo);
+    op.a2_tiled = p.stride2 == 1;
+    if (op.a2_tiled) {
+      cuuint64_t adim[2] = {(cuuint64_t)p.cin2, (cuuint64_t)n_capacity * p.hi2 * p.wi2};
+      cuuint64_t astr[1] = {(cuuint64_t)p.in2_pitch * 2};
+      cuuint32_t abox[2] = {BLOCK_K, BLOCK_M};
+      cuuint32_t aes[2] = {1, 1};
+      r = g_encode_tiled(&op.map_a2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(p.in2), adim, astr, abox, aes,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else {
+      cuuint64_t g2dim[4] = {(cuuint64_t)p.cin2, (cuuint64_t)p.wi2, (cuuint64_t)p.hi2, (cuuint64_t)n_capacity};
+      cuuint64_t g2str[3] = {(cuuint64_t)p.in2_pitch * 2, (cuuint64_t)p.wi2 * p.in2_pitch * 2,
+                             (cuuint64_t)p.hi2 * p.wi2 * p.in2_pitch * 2};
+      int lo2[2] = {0, 0}, up2[2] = {0, 0};
+      cuuint32_t es2[4] = {1, (cuuint32_t)p.stride2, (cuuint32_t)p.stride2, 1};
+      r = g_encode_im2col(&op.map_a2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p.in2), g2dim, g2str, lo2, up2, BLOCK_K,
+                          BLOCK_M, es2, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r == CUDA_SUCCESS && g_driver_version <= 13010 && (size_t)n_capacity * p.hi2 * p.wi2 * p.in2_pitch * 2 < 131072)
+        reinterpret_cast<uint64_t*>(&op.map_a2)[1] &= ~(1ull << 21);
+    }
+    if (r != CUDA_SUCCESS) return tc_fail("tensor map of the second GEMM source failed (%d)", (int)r);
+  }
   op.valid = true;
   *out = op;
   return 0;
@@ -2621,7 +2667,10 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     if (k.out_row0 + k.M > op.m_capacity) return tc_fail("batch of %d images exceeds the planned capacity", p.n);
     k.ho = p.ho; k.wo = p.wo;
     k.stride = p.stride; k.pad_h = p.pad_h; k.pad_w = p.pad_w;
-    k.kw = p.kw; k.cpb = op.cpb; k.num_kb = p.kh * p.kw * op.cpb;
+    k.kw = p.kw; k.cpb = op.cpb; k.num_kb = p.kh * p.kw * op.cpb + p.cin2_pad / BLOCK_K;
+    k.kb1 = p.kh * p.kw * op.cpb; k.stride2 = p.stride2; k.a2_tiled = op.a2_tiled ? 1 : 0;
+    k.in2_row0 = p.in_img0 * p.hi2 * p.wi2;
+    if (p.in2 && !pair) return tc_fail("only the CTA-pair kernel reads a second GEMM source");
     k.bn = op.bn; k.res_pitch = p.res_pitch; k.relu = p.relu;
     k.stages = op.stages; k.tmem_cols = op.tmem_cols; k.acc_stride = op.acc_stride;
     k.group = op.group;
@@ -2635,7 +2684,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
       const int clusters = tiles < sm_limit / 2 ? tiles : sm_limit / 2;
       static const bool profx = getenv("DML_TC_PROF") != nullptr;
       k.prof = profx ? 1 : 0;
-      launch_pdl(conv_tc2x_kernel, dim3(2 * clusters), dim3(TC2_THREADS), op.smem, s, op.map_a, op.map_b, op.map_o, op.map_r, k);
+      launch_pdl(conv_tc2x_kernel, dim3(2 * clusters), dim3(TC2_THREADS), op.smem, s, op.map_a, op.map_b, op.map_o, op.map_r, op.map_a2, k);
       if (profx) {
         cudaStreamSynchronize(s);
         static long long h[160 * 8];
@@ -2734,6 +2783,12 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     p.cin_pad = op.cin_pad;
     p.bias = reinterpret_cast<const float*>(wts + op.bias_off);
     p.relu = op.relu;
+    if (op.in2 >= 0) {
+      const Tensor& t2 = net.tensors[op.in2];
+      if (t2.buf < 0) return tc_fail("second GEMM source of %s is not an arena tensor", op.name.c_str());
+      p.in2 = ws + off_arena + ((size_t)net.bufs[t2.buf].offset * micro_batch + t2.c_off) * 2;
+      p.hi2 = t2.h; p.wi2 = t2.w; p.cin2 = op.cin2; p.in2_pitch = t2.c_pitch; p.stride2 = op.stride2; p.cin2_pad = op.cin2_pad;
+    }
     if (tc_plan_one(&plan->ops[i], p, micro_batch, TcTune()) != 0) return -1;
     if (!autotune) continue;
     // Time the candidate kernels / N tiles on the real buffers (contents do not matter) and keep the
@@ -2750,6 +2805,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     std::vector<std::array<int, 3>> seen;
     seen.push_back({plan->ops[i].version, plan->ops[i].bn, plan->ops[i].group});
     for (int version : {4, 2, 5, 6, 7}) {
+      if (op.in2 >= 0 && version != 4) continue;  // only the pair kernel reads a second GEMM source
       for (int bn : {0, 256, 128, 64}) {
         if (version == 5 && (bn != 0 || op.cout > 128 || op.res >= 0)) continue;
         if (version == 6 && bn != 0) continue;

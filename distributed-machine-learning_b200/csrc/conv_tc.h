@@ -31,6 +31,8 @@ struct TcOpPlan {
   bool has_res = false;
   bool res_direct = false;  // v4: ONE residual tile buffer with per-chunk hand-back instead of two tile buffers
   bool a_tiled = false;  // A fetched with a tiled 2D map (1x1 stride-1 convs)
+  alignas(64) CUtensorMap map_a2;  // second GEMM source (ConvParams::in2), pair kernel
+  bool a2_tiled = false;
   // v3 (halo kernel)
   int wp = 0, rows_box = 0, tiles_per_img = 0, q_valid = 0, a_stage_bytes = 0, a_stages = 0, b_stages = 0;
   // v6 (halo kernel, resident filter)

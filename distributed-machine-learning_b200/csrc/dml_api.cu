@@ -166,6 +166,11 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
       p.res_pitch = op.res >= 0 ? net.tensors[op.res].c_pitch : 0;
       p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;
       p.cin_pad = op.cin_pad; p.relu = op.relu;
+      if (op.in2 >= 0) {
+        const dml::Tensor& t2 = net.tensors[op.in2];
+        p.in2 = e->tensor_ptr(op.in2, img0);
+        p.hi2 = t2.h; p.wi2 = t2.w; p.cin2 = op.cin2; p.in2_pitch = t2.c_pitch; p.stride2 = op.stride2; p.cin2_pad = op.cin2_pad;
+      }
       int nl = 0;
       if (e->s2d && (int)oi == net.s2d.op) {
         dml::ConvParams p2 = stem_s2d_params(e, img0, cnt);
@@ -321,7 +326,9 @@ int dml_create(int device, int model, int max_batch, int micro_batch, int flags,
   if (micro_batch == 0) micro_batch = max_batch;  // whole batch per layer: large launches beat L2-resident waves here
   e->micro_batch = micro_batch < max_batch ? micro_batch : max_batch;
   std::string err;
-  if (!dml::build_net(model, e->keep_all, e->fp32 ? 4 : 2, !e->fp32, &e->net, &err)) {
+  // projection shortcuts folded into the block's last conv: tensor-core engines only (the CUDA-core kernel has one source)
+  const bool fuse_sc = e->use_tc && !e->keep_all && getenv("DML_NO_FUSE_SHORTCUT") == nullptr;
+  if (!dml::build_net(model, e->keep_all, e->fp32 ? 4 : 2, !e->fp32, fuse_sc, &e->net, &err)) {
     delete e;
     return fail(DML_EINVAL, "%s", err.c_str());
   }
@@ -420,10 +427,25 @@ int dml_load_weights(dml_engine* e, const float* blob, size_t num_floats) {
       // BN folded into the conv: s = gamma / sqrt(var + eps); W' = W*s; b' = beta + (b - mean)*s
       double s = (gamma ? (double)gamma[co] : 1.0) / std::sqrt((double)var[co] + (double)op.eps);
       bout[co] = (float)((double)beta[co] + ((bias ? (double)bias[co] : 0.0) - (double)mean[co]) * s);
+      const size_t row_k = (size_t)taps * op.cin_pad + (size_t)op.cin2_pad;  // packed K of one output channel
+      if (op.in2 >= 0) {
+        // folded projection shortcut: its own BN scale on its columns [taps * cin_pad, + cin2), its folded bias added
+        const float* K2 = blob + net.warr[op.w2_kernel].offset;  // [1][1][cin2][cout]
+        const float* bias2 = op.w2_bias >= 0 ? blob + net.warr[op.w2_bias].offset : nullptr;
+        const float* gamma2 = op.w2_gamma >= 0 ? blob + net.warr[op.w2_gamma].offset : nullptr;
+        const double s2 = (gamma2 ? (double)gamma2[co] : 1.0) /
+                          std::sqrt((double)(blob + net.warr[op.w2_var].offset)[co] + (double)op.eps2);
+        const double b2 = (double)(blob + net.warr[op.w2_beta].offset)[co] +
+                          ((bias2 ? (double)bias2[co] : 0.0) - (double)(blob + net.warr[op.w2_mean].offset)[co]) * s2;
+        bout[co] = (float)((double)bout[co] + b2);
+        for (int c = 0; c < op.cin2; ++c)
+          reinterpret_cast<uint16_t*>(host.data() + op.wpack_off)[(size_t)co * row_k + (size_t)taps * op.cin_pad + c] =
+              f32_to_bf16_rn((float)((double)K2[(size_t)c * op.cout + co] * s2));
+      }
       for (int t = 0; t < taps; ++t)
         for (int c = 0; c < op.cin; ++c) {
           float v = (float)((double)K[((size_t)t * op.cin + c) * op.cout + co] * s);
-          size_t idx = ((size_t)co * taps + t) * op.cin_pad + c;
+          size_t idx = (size_t)co * row_k + (size_t)t * op.cin_pad + c;
           if (e->fp32) reinterpret_cast<float*>(host.data() + op.wpack_off)[idx] = v;
           else reinterpret_cast<uint16_t*>(host.data() + op.wpack_off)[idx] = f32_to_bf16_rn(v);
           if (!e->fp32 && net.s2d.op >= 0 && &op == &net.ops[net.s2d.op]) {
@@ -569,8 +591,12 @@ int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* 
     int64_t out_b = op.kind == dml::OP_GAP ? (int64_t)to.c * 4 : (int64_t)to.h * to.w * to.c * e->act_bytes;
     ab = in_b + out_b + (op.res >= 0 ? out_b : 0);
     if (op.kind == dml::OP_CONV) {
-      macs = (int64_t)to.h * to.w * op.cout * op.kh * op.kw * op.cin;
-      wb = (int64_t)op.cout * op.kh * op.kw * op.cin * (e->fp32 ? 4 : 2) + op.cout * 4;
+      macs = (int64_t)to.h * to.w * op.cout * (op.kh * op.kw * op.cin + op.cin2);
+      wb = (int64_t)op.cout * (op.kh * op.kw * op.cin + op.cin2) * (e->fp32 ? 4 : 2) + op.cout * 4;
+      if (op.in2 >= 0) {  // the second source is read at stride2: only the pixels the 1x1 convolution touches
+        const dml::Tensor& t2 = net.tensors[op.in2];
+        ab += (int64_t)((t2.h + op.stride2 - 1) / op.stride2) * ((t2.w + op.stride2 - 1) / op.stride2) * t2.c * e->act_bytes;
+      }
       im = (e->use_tc && (dml::tc_supported(op) || (op.cin == 3 && op.stride == 2))) ? 1 : 0;
     }
   }

@@ -15,6 +15,7 @@ struct Builder {
   Net* net;
   bool keep_all;
   int nconv = 0;  // InceptionV3 auto-naming counter
+  bool fuse_shortcut = false;
 
   int add_warr(const std::string& name, std::initializer_list<int64_t> shape) {
     WeightArr a;
@@ -60,6 +61,7 @@ struct Builder {
     touch(op.in, idx);
     touch(op.out, idx);
     if (op.res >= 0) touch(op.res, idx);
+    if (op.in2 >= 0) touch(op.in2, idx);
     net->ops.push_back(op);
     return idx;
   }
@@ -157,10 +159,35 @@ void build_resnet50(Builder& b) {
       std::string n = "conv" + std::to_string(s + 2) + "_block" + std::to_string(blk);
       int stride = blk == 1 ? stride1[s] : 1;
       int sc = x;
-      if (blk == 1) sc = b.conv(x, -1, n + "_0_conv", n + "_0_bn", 4 * f, 1, 1, stride, false, true, true, eps, false, -1);
+      const int x0 = x;
+      Op proj;  // the projection shortcut when it is folded into _3_conv: only its weight arrays are registered here
+      const bool fold = blk == 1 && b.fuse_shortcut;
+      if (fold) {
+        const std::string cn = n + "_0_conv", bn = n + "_0_bn";
+        const int cin0 = net->tensors[x].c;
+        proj.w_kernel = b.add_warr(cn + "/kernel", {1, 1, cin0, 4 * f});
+        proj.w_bias = b.add_warr(cn + "/bias", {4 * f});
+        proj.w_gamma = b.add_warr(bn + "/gamma", {4 * f});
+        proj.w_beta = b.add_warr(bn + "/beta", {4 * f});
+        proj.w_mean = b.add_warr(bn + "/moving_mean", {4 * f});
+        proj.w_var = b.add_warr(bn + "/moving_variance", {4 * f});
+        sc = -1;
+      } else if (blk == 1) {
+        sc = b.conv(x, -1, n + "_0_conv", n + "_0_bn", 4 * f, 1, 1, stride, false, true, true, eps, false, -1);
+      }
       int y = b.conv(x, -1, n + "_1_conv", n + "_1_bn", f, 1, 1, stride, false, true, true, eps, true, -1);
       y = b.conv(y, -1, n + "_2_conv", n + "_2_bn", f, 3, 3, 1, true, true, true, eps, true, -1);
       x = b.conv(y, -1, n + "_3_conv", n + "_3_bn", 4 * f, 1, 1, 1, false, true, true, eps, true, sc);
+      if (fold) {
+        const int oi = (int)net->ops.size() - 1;
+        Op& o3 = net->ops[oi];
+        o3.in2 = x0; o3.cin2 = net->tensors[x0].c; o3.stride2 = stride; o3.eps2 = eps;
+        o3.w2_kernel = proj.w_kernel; o3.w2_bias = proj.w_bias; o3.w2_gamma = proj.w_gamma;
+        o3.w2_beta = proj.w_beta; o3.w2_mean = proj.w_mean; o3.w2_var = proj.w_var;
+        b.touch(x0, oi);  // the block input stays alive until the folded conv has read it
+        const Tensor& to = net->tensors[x];
+        net->conv_macs += (int64_t)to.h * to.w * to.c * o3.cin2;
+      }
       net->tensors[x].name = n + "_out";
     }
   }
@@ -301,8 +328,9 @@ void plan_weights(Net* net, int wbytes, bool tc_pad) {
   for (Op& op : net->ops) {
     if (op.kind != OP_CONV) continue;
     op.cin_pad = (tc_pad && op.cin >= 16) ? (int)align_up(op.cin, 64) : op.cin;
+    op.cin2_pad = op.in2 >= 0 ? (int)align_up(op.cin2, 64) : 0;
     op.wpack_off = off;
-    off = align_up(off + (int64_t)op.cout * op.kh * op.kw * op.cin_pad * wbytes, 256);
+    off = align_up(off + (int64_t)op.cout * (op.kh * op.kw * op.cin_pad + op.cin2_pad) * wbytes, 256);
     op.bias_off = off;
     off = align_up(off + (int64_t)op.cout * 4, 256);
   }
@@ -328,10 +356,11 @@ void plan_weights(Net* net, int wbytes, bool tc_pad) {
   net->weights_bytes = off;
 }
 
-bool build(int model, bool keep_all, int wbytes, bool tc_pad, bool spec_only, Net* net, std::string* err) {
+bool build(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut, bool spec_only, Net* net, std::string* err) {
   *net = Net();
   net->model = model;
   Builder b{net, keep_all};
+  b.fuse_shortcut = fuse_shortcut && !keep_all && tc_pad;
   Tensor in;
   in.name = "input";
   in.buf = -1;
@@ -356,11 +385,11 @@ bool build(int model, bool keep_all, int wbytes, bool tc_pad, bool spec_only, Ne
 
 }  // namespace
 
-bool build_net(int model, bool keep_all, int wbytes, bool tc_pad, Net* net, std::string* err) {
-  return build(model, keep_all, wbytes, tc_pad, false, net, err);
+bool build_net(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut, Net* net, std::string* err) {
+  return build(model, keep_all, wbytes, tc_pad, fuse_shortcut, false, net, err);
 }
 bool build_weight_spec(int model, Net* net, std::string* err) {
-  return build(model, true, 4, false, true, net, err);
+  return build(model, true, 4, false, false, true, net, err);
 }
 
 }  // namespace dml

@@ -15,6 +15,9 @@ struct ConvParams {
   int ho, wo, cout, out_pitch, res_pitch;
   int kh, kw, stride, pad_h, pad_w, cin_pad;
   int relu;
+  // second GEMM source (graph.h, Op::in2): a 1x1 convolution of stride stride2 over in2, accumulated into the same output
+  const void* in2 = nullptr;
+  int hi2 = 0, wi2 = 0, cin2 = 0, in2_pitch = 0, stride2 = 1, cin2_pad = 0;
   int in_img0 = 0;   // tcgen05 path: first image / first output row of this launch inside the
   int out_row0 = 0;  // planned tensor maps (the pointers above are already offset for the CUDA-core path)
 };

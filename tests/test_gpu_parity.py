@@ -104,6 +104,37 @@ def test_results_do_not_depend_on_micro_batch(images):
     assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
 
 
+def test_folded_projection_shortcut_matches_separate_convs(images, monkeypatch):
+    """ResNet50's projection shortcuts run as a second GEMM source of the block's last conv (graph.h, Op::in2).
+    Against the same engine with the shortcut as its own conv + residual add (DML_NO_FUSE_SHORTCUT), on weights with
+    non-trivial biases / BN statistics: the only difference is that the shortcut is no longer rounded to bf16."""
+    from oracle import models_ref
+    kw = pkg("keras_weights")
+    W = kw.generate("ResNet50", "folding_stress", 5)
+    sel = images[20:45]   # 25 images: partial tiles in conv4 / conv5
+    outs = []
+    for fuse in (True, False):
+        if fuse:
+            monkeypatch.delenv("DML_NO_FUSE_SHORTCUT", raising=False)
+        else:
+            monkeypatch.setenv("DML_NO_FUSE_SHORTCUT", "1")
+        eng = pkg("engine").Engine("ResNet50", max_batch=32, weights=W)
+        try:
+            names = [o[0] for o in eng.ops()]
+            assert ("conv2_block1_0_conv" in names) == (not fuse)
+            eng.predict_images(sel)
+            outs.append(eng.logits(len(sel)).cpu().numpy().copy())
+        finally:
+            eng.close()
+    _, ref = models_ref.predict_arrays("ResNet50", sel, W, batch=25)
+    scale = np.abs(ref).max()
+    err_f, err_s = np.abs(outs[0] - ref).max() / scale, np.abs(outs[1] - ref).max() / scale
+    print(f"\nlogits vs fp32 oracle: folded {err_f:.3e}, separate {err_s:.3e}; folded vs separate {np.abs(outs[0] - outs[1]).max() / scale:.3e}")
+    assert np.abs(outs[0] - outs[1]).max() / scale <= 2e-2
+    assert err_f <= max(2e-2, 1.5 * err_s)
+    assert np.array_equal(outs[0].argmax(1), outs[1].argmax(1))
+
+
 def test_folding_stress_fp32(images):
     """Non-trivial biases and BN statistics: folding checked in fp32 mode."""
     from oracle import models_ref
