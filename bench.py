@@ -241,6 +241,8 @@ def run_b200(args):
         ops = eng.ops()
         kinds = {0: "conv", 1: "maxpool", 2: "avgpool", 3: "gap", 4: "dense", 5: "softmax_top5"}
         for (name, kind, impl, macs, ab, wb), t in zip(ops, ms):
+            if kind == 0 and macs == 0:
+                continue  # follower of a merged pair of 1x1 convolutions: no launch of its own, reported by its leader
             key = kinds[kind] + ("_tcgen05" if kind == 0 and impl == 1 else ("_cuda_core" if kind == 0 else ""))
             d = per_kind.setdefault(key, {"ms": 0.0, "flop": 0.0, "bytes": 0.0, "launch_sites": 0})
             d["ms"] += float(t)

@@ -2764,9 +2764,10 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     return tc_fail("autotune: cudaEventCreate failed");
   for (size_t i = 0; i < net.ops.size(); ++i) {
     const Op& op = net.ops[i];
-    if (!tc_supported(op)) continue;
+    if (!tc_supported(op) || op.skip) continue;  // a follower of a merged 1x1 pair is computed by its leader
     const Tensor& ti = net.tensors[op.in];
-    const Tensor& to = net.tensors[op.out];
+    const Tensor& to = net.tensors[op.merged_out >= 0 ? op.merged_out : op.out];
+    const int cout_x = op.merged_cout > 0 ? op.merged_cout : op.cout;
     if (ti.buf < 0) continue;
     ConvParams p{};
     p.in = ws + off_arena + ((size_t)net.bufs[ti.buf].offset * micro_batch + ti.c_off) * 2;
@@ -2778,7 +2779,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
       p.res_pitch = tr.c_pitch;
     }
     p.n = micro_batch; p.hi = ti.h; p.wi = ti.w; p.cin = op.cin; p.in_pitch = ti.c_pitch;
-    p.ho = to.h; p.wo = to.w; p.cout = op.cout; p.out_pitch = to.c_pitch;
+    p.ho = to.h; p.wo = to.w; p.cout = cout_x; p.out_pitch = to.c_pitch;
     p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;
     p.cin_pad = op.cin_pad;
     p.bias = reinterpret_cast<const float*>(wts + op.bias_off);
@@ -2807,9 +2808,9 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     for (int version : {4, 2, 5, 6, 7}) {
       if (op.in2 >= 0 && version != 4) continue;  // only the pair kernel reads a second GEMM source
       for (int bn : {0, 256, 128, 64}) {
-        if (version == 5 && (bn != 0 || op.cout > 128 || op.res >= 0)) continue;
+        if (version == 5 && (bn != 0 || cout_x > 128 || op.res >= 0)) continue;
         if (version == 6 && bn != 0) continue;
-        if (bn && (op.cout % bn != 0 || bn > op.cout)) continue;
+        if (bn && (cout_x % bn != 0 || bn > cout_x)) continue;
         for (int g : {0, 1, 2, 3, 4}) {
           if (version >= 5 && g != 0) continue;
           TcTune t;
@@ -2829,7 +2830,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     }
     if (op.res >= 0) {  // residual layers: also with two whole residual tile buffers instead of the chunked single one
       for (int bn : {0, 256, 128}) {
-        if (bn && (op.cout % bn != 0 || bn > op.cout)) continue;
+        if (bn && (cout_x % bn != 0 || bn > cout_x)) continue;
         TcTune t;
         t.version = 4; t.bn = bn; t.res_direct = 1;
         TcOpPlan cand;

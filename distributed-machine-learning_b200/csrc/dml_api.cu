@@ -151,8 +151,11 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
   const dml::Net& net = e->net;
   for (size_t oi = 0; oi < net.ops.size(); ++oi) {
     const dml::Op& op = net.ops[oi];
+    if (op.skip) continue;  // computed by its leader (Op::merge_with)
+    const int out_t = op.merged_out >= 0 ? op.merged_out : op.out;
+    const int cout_x = op.merged_cout > 0 ? op.merged_cout : op.cout;
     const dml::Tensor& ti = net.tensors[op.in];
-    const dml::Tensor& to = net.tensors[op.out];
+    const dml::Tensor& to = net.tensors[out_t];
     e->prof_begin((int)oi, s);
     if (op.kind == dml::OP_CONV) {
       dml::ConvParams p{};
@@ -160,9 +163,9 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
       p.w = e->wts + op.wpack_off;
       p.bias = reinterpret_cast<const float*>(e->wts + op.bias_off);
       p.res = op.res >= 0 ? e->tensor_ptr(op.res, img0) : nullptr;
-      p.out = e->tensor_ptr(op.out, img0);
+      p.out = e->tensor_ptr(out_t, img0);
       p.n = cnt; p.hi = ti.h; p.wi = ti.w; p.cin = op.cin; p.in_pitch = ti.c_pitch;
-      p.ho = to.h; p.wo = to.w; p.cout = op.cout; p.out_pitch = to.c_pitch;
+      p.ho = to.h; p.wo = to.w; p.cout = cout_x; p.out_pitch = to.c_pitch;
       p.res_pitch = op.res >= 0 ? net.tensors[op.res].c_pitch : 0;
       p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;
       p.cin_pad = op.cin_pad; p.relu = op.relu;
@@ -585,14 +588,24 @@ int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* 
   } else {
     const dml::Op& op = net.ops[i];
     const dml::Tensor& ti = net.tensors[op.in];
-    const dml::Tensor& to = net.tensors[op.out];
+    const dml::Tensor& to = net.tensors[op.merged_out >= 0 ? op.merged_out : op.out];
+    const int cout_x = op.merged_cout > 0 ? op.merged_cout : op.cout;
     nm = op.name; k = (int)op.kind;
+    if (op.skip) {  // a follower of a merged 1x1 pair: its work is reported by the leader
+      if (name && name_cap > 0) snprintf(name, name_cap, "%s", nm.c_str());
+      if (kind) *kind = k;
+      if (impl) *impl = e->use_tc ? 1 : 0;
+      if (macs_per_img) *macs_per_img = 0;
+      if (act_bytes_per_img) *act_bytes_per_img = 0;
+      if (weight_bytes) *weight_bytes = 0;
+      return 0;
+    }
     int64_t in_b = (int64_t)ti.h * ti.w * ti.c * e->act_bytes;
     int64_t out_b = op.kind == dml::OP_GAP ? (int64_t)to.c * 4 : (int64_t)to.h * to.w * to.c * e->act_bytes;
     ab = in_b + out_b + (op.res >= 0 ? out_b : 0);
     if (op.kind == dml::OP_CONV) {
-      macs = (int64_t)to.h * to.w * op.cout * (op.kh * op.kw * op.cin + op.cin2);
-      wb = (int64_t)op.cout * (op.kh * op.kw * op.cin + op.cin2) * (e->fp32 ? 4 : 2) + op.cout * 4;
+      macs = (int64_t)to.h * to.w * cout_x * (op.kh * op.kw * op.cin + op.cin2);
+      wb = (int64_t)cout_x * (op.kh * op.kw * op.cin + op.cin2) * (e->fp32 ? 4 : 2) + cout_x * 4;
       if (op.in2 >= 0) {  // the second source is read at stride2: only the pixels the 1x1 convolution touches
         const dml::Tensor& t2 = net.tensors[op.in2];
         ab += (int64_t)((t2.h + op.stride2 - 1) / op.stride2) * ((t2.w + op.stride2 - 1) / op.stride2) * t2.c * e->act_bytes;

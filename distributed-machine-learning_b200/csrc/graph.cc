@@ -103,6 +103,35 @@ struct Builder {
     push(op);
     return out;
   }
+  // Two sibling 1x1 reductions of tensor x (f1 and f2 filters) whose outputs are the channel slices [0, f1) and [f1, f1+f2)
+  // of one tensor.  red1 / red2 create them at their place in Keras' layer order; with fuse_shortcut the second becomes a
+  // follower of the first (Op::merge_with) and the first computes both.
+  struct Pair { int t = -1, v1 = -1, v2 = -1, op1 = -1, f1 = 0, f2 = 0; };
+  Pair pair_begin(int x, const std::string& name, int f1, int f2) {
+    Pair p;
+    p.f1 = f1; p.f2 = f2;
+    if (!fuse_shortcut) return p;
+    const Tensor tx = net->tensors[x];
+    p.t = new_tensor(name, tx.h, tx.w, f1 + f2);
+    p.v1 = view(p.t, name + ":a", 0, f1);
+    p.v2 = view(p.t, name + ":b", f1, f2);
+    return p;
+  }
+  int red1(int x, Pair& p) {
+    int out = cb(x, p.v1, p.f1, 1, 1);
+    p.op1 = (int)net->ops.size() - 1;
+    return out;
+  }
+  int red2(int x, Pair& p) {
+    int out = cb(x, p.v2, p.f2, 1, 1);
+    if (p.t >= 0) {
+      const int i2 = (int)net->ops.size() - 1;
+      Op& lead = net->ops[p.op1];
+      lead.merge_with = i2; lead.merged_cout = p.f1 + p.f2; lead.merged_out = p.t;
+      net->ops[i2].skip = true;
+    }
+    return out;
+  }
   // InceptionV3 conv2d_bn: Conv2D(no bias) -> BN(scale=False, eps 1e-3) -> ReLU
   int cb(int in, int out, int f, int kh, int kw, bool same = true, int stride = 1) {
     int i = nconv++;
@@ -213,9 +242,10 @@ void build_inception_v3(Builder& b) {
     const Tensor tx = net->tensors[x];
     int cat = b.new_tensor(n, tx.h, tx.w, 64 + 64 + 96 + pool_f[i]);
     b.cb(x, b.view(cat, n + ":b1", 0, 64), 64, 1, 1);
-    int t = b.cb(x, -1, 48, 1, 1);
+    Builder::Pair pr = b.pair_begin(x, n + ":red", 48, 64);
+    int t = b.red1(x, pr);
     b.cb(t, b.view(cat, n + ":b5", 64, 64), 64, 5, 5);
-    t = b.cb(x, -1, 64, 1, 1);
+    t = b.red2(x, pr);
     t = b.cb(t, -1, 96, 3, 3);
     b.cb(t, b.view(cat, n + ":b3d", 128, 96), 96, 3, 3);
     t = b.pool(OP_AVGPOOL, x, -1, n + ":avgpool", 3, 1, 1);
@@ -240,10 +270,11 @@ void build_inception_v3(Builder& b) {
     int c = c7[i];
     int cat = b.new_tensor(n, tx.h, tx.w, 768);
     b.cb(x, b.view(cat, n + ":b1", 0, 192), 192, 1, 1);
-    int t = b.cb(x, -1, c, 1, 1);
+    Builder::Pair pr = b.pair_begin(x, n + ":red", c, c);
+    int t = b.red1(x, pr);
     t = b.cb(t, -1, c, 1, 7);
     b.cb(t, b.view(cat, n + ":b7", 192, 192), 192, 7, 1);
-    t = b.cb(x, -1, c, 1, 1);
+    t = b.red2(x, pr);
     t = b.cb(t, -1, c, 7, 1);
     t = b.cb(t, -1, c, 1, 7);
     t = b.cb(t, -1, c, 7, 1);
@@ -256,9 +287,10 @@ void build_inception_v3(Builder& b) {
     const Tensor tx = net->tensors[x];
     int ho = (tx.h - 3) / 2 + 1;
     int cat = b.new_tensor("mixed8", ho, ho, 320 + 192 + tx.c);
-    int t = b.cb(x, -1, 192, 1, 1);
+    Builder::Pair pr = b.pair_begin(x, "mixed8:red", 192, 192);
+    int t = b.red1(x, pr);
     b.cb(t, b.view(cat, "mixed8:b3", 0, 320), 320, 3, 3, false, 2);
-    t = b.cb(x, -1, 192, 1, 1);
+    t = b.red2(x, pr);
     t = b.cb(t, -1, 192, 1, 7);
     t = b.cb(t, -1, 192, 7, 1);
     b.cb(t, b.view(cat, "mixed8:b7x3", 320, 192), 192, 3, 3, false, 2);
@@ -270,10 +302,11 @@ void build_inception_v3(Builder& b) {
     const Tensor tx = net->tensors[x];
     int cat = b.new_tensor(n, tx.h, tx.w, 2048);
     b.cb(x, b.view(cat, n + ":b1", 0, 320), 320, 1, 1);
-    int t = b.cb(x, -1, 384, 1, 1);
+    Builder::Pair pr = b.pair_begin(x, n + ":red", 384, 448);
+    int t = b.red1(x, pr);
     b.cb(t, b.view(cat, n + ":b3a", 320, 384), 384, 1, 3);
     b.cb(t, b.view(cat, n + ":b3b", 704, 384), 384, 3, 1);
-    t = b.cb(x, -1, 448, 1, 1);
+    t = b.red2(x, pr);
     t = b.cb(t, -1, 384, 3, 3);
     b.cb(t, b.view(cat, n + ":bda", 1088, 384), 384, 1, 3);
     b.cb(t, b.view(cat, n + ":bdb", 1472, 384), 384, 3, 1);
@@ -329,10 +362,19 @@ void plan_weights(Net* net, int wbytes, bool tc_pad) {
     if (op.kind != OP_CONV) continue;
     op.cin_pad = (tc_pad && op.cin >= 16) ? (int)align_up(op.cin, 64) : op.cin;
     op.cin2_pad = op.in2 >= 0 ? (int)align_up(op.cin2, 64) : 0;
+    if (op.skip) continue;  // a follower's rows were placed right behind its leader's
+    const int rows = op.merged_cout > 0 ? op.merged_cout : op.cout;
+    const int64_t row_bytes = (int64_t)(op.kh * op.kw * op.cin_pad + op.cin2_pad) * wbytes;
     op.wpack_off = off;
-    off = align_up(off + (int64_t)op.cout * (op.kh * op.kw * op.cin_pad + op.cin2_pad) * wbytes, 256);
+    off = align_up(off + rows * row_bytes, 256);
     op.bias_off = off;
-    off = align_up(off + (int64_t)op.cout * 4, 256);
+    off = align_up(off + (int64_t)rows * 4, 256);
+    if (op.merge_with >= 0) {
+      Op& f = net->ops[op.merge_with];
+      f.cin_pad = op.cin_pad;
+      f.wpack_off = op.wpack_off + op.cout * row_bytes;
+      f.bias_off = op.bias_off + (int64_t)op.cout * 4;
+    }
   }
   // floor division by 2 of (tap - pad): cells a in [a_min, a_max] of the space-to-depth grid
   auto fdiv2 = [](int v) { return v >= 0 ? v / 2 : -((-v + 1) / 2); };

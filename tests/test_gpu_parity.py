@@ -135,6 +135,29 @@ def test_folded_projection_shortcut_matches_separate_convs(images, monkeypatch):
     assert np.array_equal(outs[0].argmax(1), outs[1].argmax(1))
 
 
+def test_merged_sibling_reductions_are_bit_identical(images, monkeypatch):
+    """InceptionV3's two sibling 1x1 branch reductions of a block run as one GEMM (graph.h, Op::merge_with): every output
+    channel sees the same K loop, so the logits must not change by a single bit against the separate convolutions."""
+    kw = pkg("keras_weights")
+    W = kw.generate("InceptionV3", "folding_stress", 11)
+    sel = images[50:69]
+    outs = []
+    for fuse in (True, False):
+        if fuse:
+            monkeypatch.delenv("DML_NO_FUSE_SHORTCUT", raising=False)
+        else:
+            monkeypatch.setenv("DML_NO_FUSE_SHORTCUT", "1")
+        eng = pkg("engine").Engine("InceptionV3", max_batch=24, weights=W)
+        try:
+            followers = [o[0] for o in eng.ops() if o[1] == 0 and o[3] == 0]
+            assert (len(followers) == 10) == fuse, followers
+            eng.predict_images(sel)
+            outs.append(eng.logits(len(sel)).cpu().numpy().copy())
+        finally:
+            eng.close()
+    assert np.array_equal(outs[0], outs[1])
+
+
 def test_folding_stress_fp32(images):
     """Non-trivial biases and BN statistics: folding checked in fp32 mode."""
     from oracle import models_ref
