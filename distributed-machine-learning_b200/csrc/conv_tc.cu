@@ -2771,7 +2771,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     if (ti.buf < 0) continue;
     ConvParams p{};
     p.in = ws + off_arena + ((size_t)net.bufs[ti.buf].offset * micro_batch + ti.c_off) * 2;
-    p.w = wts + op.wpack_off;
+    p.w = wts + op.merged_w_off;
     p.out = ws + off_arena + ((size_t)net.bufs[to.buf].offset * micro_batch + to.c_off) * 2;
     if (op.res >= 0) {
       const Tensor& tr = net.tensors[op.res];
@@ -2782,7 +2782,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     p.ho = to.h; p.wo = to.w; p.cout = cout_x; p.out_pitch = to.c_pitch;
     p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;
     p.cin_pad = op.cin_pad;
-    p.bias = reinterpret_cast<const float*>(wts + op.bias_off);
+    p.bias = reinterpret_cast<const float*>(wts + op.merged_b_off);
     p.relu = op.relu;
     if (op.in2 >= 0) {
       const Tensor& t2 = net.tensors[op.in2];

@@ -160,8 +160,8 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
     if (op.kind == dml::OP_CONV) {
       dml::ConvParams p{};
       p.in = e->tensor_ptr(op.in, img0);
-      p.w = e->wts + op.wpack_off;
-      p.bias = reinterpret_cast<const float*>(e->wts + op.bias_off);
+      p.w = e->wts + op.merged_w_off;  // = wpack_off unless the op leads a merged group (its rows need not come first)
+      p.bias = reinterpret_cast<const float*>(e->wts + op.merged_b_off);
       p.res = op.res >= 0 ? e->tensor_ptr(op.res, img0) : nullptr;
       p.out = e->tensor_ptr(out_t, img0);
       p.n = cnt; p.hi = ti.h; p.wi = ti.w; p.cin = op.cin; p.in_pitch = ti.c_pitch;

@@ -127,8 +127,50 @@ struct Builder {
     if (p.t >= 0) {
       const int i2 = (int)net->ops.size() - 1;
       Op& lead = net->ops[p.op1];
-      lead.merge_with = i2; lead.merged_cout = p.f1 + p.f2; lead.merged_out = p.t;
+      lead.followers.push_back(i2); lead.merged_cout = p.f1 + p.f2; lead.merged_out = p.t;
       net->ops[i2].skip = true;
+      net->ops[i2].merge_row0 = p.f1;
+    }
+    return out;
+  }
+  // Block head with a 1x1 branch that goes straight into the concat: [reduction 1 | reduction 2 | concat] share ONE buffer,
+  // the two reductions in R = f1 + f2 scratch channels in FRONT of the concat, so that (red1, red2, branch1x1) are one
+  // contiguous channel range = one GEMM.  The block's output tensor is the view behind the scratch channels.
+  struct Head { int cat = -1, b1 = -1, v1 = -1, v2 = -1, merged = -1, lead = -1, R = 0, f1 = 0, f2 = 0, fb1 = 0; };
+  Head head_begin(int x, const std::string& n, int fb1, int f1, int f2, int ccat) {
+    Head h;
+    h.f1 = f1; h.f2 = f2; h.fb1 = fb1;
+    const Tensor tx = net->tensors[x];
+    if (!fuse_shortcut) {
+      h.cat = new_tensor(n, tx.h, tx.w, ccat);
+      h.b1 = view(h.cat, n + ":b1", 0, fb1);
+      return h;
+    }
+    h.R = f1 + f2;
+    const int buf = new_tensor(n + ":buf", tx.h, tx.w, h.R + ccat);
+    h.cat = view(buf, n, h.R, ccat);
+    h.b1 = view(buf, n + ":b1", h.R, fb1);
+    h.v1 = view(buf, n + ":red:a", 0, f1);
+    h.v2 = view(buf, n + ":red:b", f1, f2);
+    h.merged = view(buf, n + ":head", 0, h.R + fb1);
+    return h;
+  }
+  int cat_view(const Head& h, const std::string& name, int c_off, int c) { return view(h.cat, name, h.R + c_off, c); }
+  void head_b1(int x, Head& h) {  // branch1x1: first in Keras' layer order, so it leads the group
+    cb(x, h.b1, h.fb1, 1, 1);
+    h.lead = (int)net->ops.size() - 1;
+    if (h.merged >= 0) {
+      Op& o = net->ops[h.lead];
+      o.merged_cout = h.R + h.fb1; o.merged_out = h.merged; o.merge_row0 = h.R;
+    }
+  }
+  int head_red(int x, Head& h, int which) {
+    int out = cb(x, which == 0 ? h.v1 : h.v2, which == 0 ? h.f1 : h.f2, 1, 1);
+    if (h.merged >= 0) {
+      const int i = (int)net->ops.size() - 1;
+      net->ops[i].skip = true;
+      net->ops[i].merge_row0 = which == 0 ? 0 : h.f1;
+      net->ops[h.lead].followers.push_back(i);
     }
     return out;
   }
@@ -240,17 +282,16 @@ void build_inception_v3(Builder& b) {
   for (int i = 0; i < 3; ++i) {  // mixed0..2, 35x35
     std::string n = "mixed" + std::to_string(i);
     const Tensor tx = net->tensors[x];
-    int cat = b.new_tensor(n, tx.h, tx.w, 64 + 64 + 96 + pool_f[i]);
-    b.cb(x, b.view(cat, n + ":b1", 0, 64), 64, 1, 1);
-    Builder::Pair pr = b.pair_begin(x, n + ":red", 48, 64);
-    int t = b.red1(x, pr);
-    b.cb(t, b.view(cat, n + ":b5", 64, 64), 64, 5, 5);
-    t = b.red2(x, pr);
+    Builder::Head hd = b.head_begin(x, n, 64, 48, 64, 64 + 64 + 96 + pool_f[i]);
+    b.head_b1(x, hd);
+    int t = b.head_red(x, hd, 0);
+    b.cb(t, b.cat_view(hd, n + ":b5", 64, 64), 64, 5, 5);
+    t = b.head_red(x, hd, 1);
     t = b.cb(t, -1, 96, 3, 3);
-    b.cb(t, b.view(cat, n + ":b3d", 128, 96), 96, 3, 3);
+    b.cb(t, b.cat_view(hd, n + ":b3d", 128, 96), 96, 3, 3);
     t = b.pool(OP_AVGPOOL, x, -1, n + ":avgpool", 3, 1, 1);
-    b.cb(t, b.view(cat, n + ":bp", 224, pool_f[i]), pool_f[i], 1, 1);
-    x = cat;
+    b.cb(t, b.cat_view(hd, n + ":bp", 224, pool_f[i]), pool_f[i], 1, 1);
+    x = hd.cat;
   }
   {  // mixed3, 17x17
     const Tensor tx = net->tensors[x];
@@ -268,20 +309,19 @@ void build_inception_v3(Builder& b) {
     std::string n = "mixed" + std::to_string(i + 4);
     const Tensor tx = net->tensors[x];
     int c = c7[i];
-    int cat = b.new_tensor(n, tx.h, tx.w, 768);
-    b.cb(x, b.view(cat, n + ":b1", 0, 192), 192, 1, 1);
-    Builder::Pair pr = b.pair_begin(x, n + ":red", c, c);
-    int t = b.red1(x, pr);
+    Builder::Head hd = b.head_begin(x, n, 192, c, c, 768);
+    b.head_b1(x, hd);
+    int t = b.head_red(x, hd, 0);
     t = b.cb(t, -1, c, 1, 7);
-    b.cb(t, b.view(cat, n + ":b7", 192, 192), 192, 7, 1);
-    t = b.red2(x, pr);
+    b.cb(t, b.cat_view(hd, n + ":b7", 192, 192), 192, 7, 1);
+    t = b.head_red(x, hd, 1);
     t = b.cb(t, -1, c, 7, 1);
     t = b.cb(t, -1, c, 1, 7);
     t = b.cb(t, -1, c, 7, 1);
-    b.cb(t, b.view(cat, n + ":b7d", 384, 192), 192, 1, 7);
+    b.cb(t, b.cat_view(hd, n + ":b7d", 384, 192), 192, 1, 7);
     t = b.pool(OP_AVGPOOL, x, -1, n + ":avgpool", 3, 1, 1);
-    b.cb(t, b.view(cat, n + ":bp", 576, 192), 192, 1, 1);
-    x = cat;
+    b.cb(t, b.cat_view(hd, n + ":bp", 576, 192), 192, 1, 1);
+    x = hd.cat;
   }
   {  // mixed8, 8x8
     const Tensor tx = net->tensors[x];
@@ -300,19 +340,18 @@ void build_inception_v3(Builder& b) {
   for (int i = 9; i <= 10; ++i) {  // mixed9, mixed10, 8x8
     std::string n = "mixed" + std::to_string(i);
     const Tensor tx = net->tensors[x];
-    int cat = b.new_tensor(n, tx.h, tx.w, 2048);
-    b.cb(x, b.view(cat, n + ":b1", 0, 320), 320, 1, 1);
-    Builder::Pair pr = b.pair_begin(x, n + ":red", 384, 448);
-    int t = b.red1(x, pr);
-    b.cb(t, b.view(cat, n + ":b3a", 320, 384), 384, 1, 3);
-    b.cb(t, b.view(cat, n + ":b3b", 704, 384), 384, 3, 1);
-    t = b.red2(x, pr);
+    Builder::Head hd = b.head_begin(x, n, 320, 384, 448, 2048);
+    b.head_b1(x, hd);
+    int t = b.head_red(x, hd, 0);
+    b.cb(t, b.cat_view(hd, n + ":b3a", 320, 384), 384, 1, 3);
+    b.cb(t, b.cat_view(hd, n + ":b3b", 704, 384), 384, 3, 1);
+    t = b.head_red(x, hd, 1);
     t = b.cb(t, -1, 384, 3, 3);
-    b.cb(t, b.view(cat, n + ":bda", 1088, 384), 384, 1, 3);
-    b.cb(t, b.view(cat, n + ":bdb", 1472, 384), 384, 3, 1);
+    b.cb(t, b.cat_view(hd, n + ":bda", 1088, 384), 384, 1, 3);
+    b.cb(t, b.cat_view(hd, n + ":bdb", 1472, 384), 384, 3, 1);
     t = b.pool(OP_AVGPOOL, x, -1, n + ":avgpool", 3, 1, 1);
-    b.cb(t, b.view(cat, n + ":bp", 1856, 192), 192, 1, 1);
-    x = cat;
+    b.cb(t, b.cat_view(hd, n + ":bp", 1856, 192), 192, 1, 1);
+    x = hd.cat;
   }
   b.head(x);
 }
@@ -365,15 +404,17 @@ void plan_weights(Net* net, int wbytes, bool tc_pad) {
     if (op.skip) continue;  // a follower's rows were placed right behind its leader's
     const int rows = op.merged_cout > 0 ? op.merged_cout : op.cout;
     const int64_t row_bytes = (int64_t)(op.kh * op.kw * op.cin_pad + op.cin2_pad) * wbytes;
-    op.wpack_off = off;
+    op.merged_w_off = off;
     off = align_up(off + rows * row_bytes, 256);
-    op.bias_off = off;
+    op.merged_b_off = off;
     off = align_up(off + (int64_t)rows * 4, 256);
-    if (op.merge_with >= 0) {
-      Op& f = net->ops[op.merge_with];
+    op.wpack_off = op.merged_w_off + op.merge_row0 * row_bytes;
+    op.bias_off = op.merged_b_off + (int64_t)op.merge_row0 * 4;
+    for (int fi : op.followers) {
+      Op& f = net->ops[fi];
       f.cin_pad = op.cin_pad;
-      f.wpack_off = op.wpack_off + op.cout * row_bytes;
-      f.bias_off = op.bias_off + (int64_t)op.cout * 4;
+      f.wpack_off = op.merged_w_off + f.merge_row0 * row_bytes;
+      f.bias_off = op.merged_b_off + (int64_t)f.merge_row0 * 4;
     }
   }
   // floor division by 2 of (tap - pad): cells a in [a_min, a_max] of the space-to-depth grid

@@ -49,11 +49,15 @@ struct Op {
   // Second GEMM source (ResNet50 projection shortcut folded into the block's last conv): out = relu(W x + W2 x2 + b + b2)
   // with x2 = tensor in2 read through a 1x1 convolution of stride stride2.  The packed weight rows are
   // [taps * cin_pad | cin2_pad] and the bias is the sum of both folded biases.  in2 < 0: none.
-  // Sibling 1x1 convolutions of one input run as ONE GEMM (InceptionV3 branch reductions): the leader executes with
-  // merged_cout output channels into tensor merged_out (the followers' outputs are channel slices of it), its packed
-  // weight / bias rows are followed directly by the follower's; the follower (skip = true) only carries its weight arrays.
+  // Sibling 1x1 convolutions of one input run as ONE GEMM (InceptionV3 branch heads): the leader executes with
+  // merged_cout output channels into tensor merged_out (every member's output is a channel slice of it); the members'
+  // packed weight / bias rows sit in one block in slice order (merge_row0); a follower (skip = true) only carries its
+  // weight arrays.
   bool skip = false;
-  int merge_with = -1, merged_cout = 0, merged_out = -1;
+  std::vector<int> followers;            // leader: the ops whose outputs it also computes
+  int merged_cout = 0, merged_out = -1;  // leader: summed Cout and the tensor that holds all slices
+  int merge_row0 = 0;                    // leader and followers: first row of this op inside the merged weight / bias block
+  int64_t merged_w_off = 0, merged_b_off = 0;  // leader: start of the merged block (bytes into the weights buffer)
   int in2 = -1, cin2 = 0, cin2_pad = 0, stride2 = 1;
   int w2_kernel = -1, w2_bias = -1, w2_gamma = -1, w2_beta = -1, w2_mean = -1, w2_var = -1;
   float eps2 = 0.f;
@@ -90,7 +94,7 @@ struct Net {
 // wbytes: bytes per packed conv weight element (2 = bf16, 4 = fp32 check mode).
 // tc_pad: pad Cin of tensor-core-eligible convs to a multiple of 64.
 // fuse_shortcut: ResNet50's projection shortcuts become a second GEMM source of the block's last conv (Op::in2) and
-// InceptionV3's sibling 1x1 branch reductions become one GEMM (Op::merge_with).
+// InceptionV3's sibling 1x1 branch heads become one GEMM (Op::followers).
 bool build_net(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut, Net* net, std::string* err);
 
 // Only the weight-array list (cheap; for dml_model_* queries).
