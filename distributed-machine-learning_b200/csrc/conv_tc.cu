@@ -2737,15 +2737,17 @@ namespace {
 float time_plan(const TcOpPlan& op, const ConvParams& p, cudaEvent_t e0, cudaEvent_t e1) {
   if (launch_conv_tc_plan(op, p, nullptr) != 0) return 1e30f;
   float best = 1e30f;
-  for (int rep = 0; rep < 3; ++rep) {
+  static const int reps = getenv("DML_TUNE_REPS") ? atoi(getenv("DML_TUNE_REPS")) : 3;      // experiments only
+  static const int burst = getenv("DML_TUNE_BURST") ? atoi(getenv("DML_TUNE_BURST")) : 4;
+  for (int rep = 0; rep < reps; ++rep) {
     cudaEventRecord(e0, nullptr);
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < burst; ++i)
       if (launch_conv_tc_plan(op, p, nullptr) != 0) return 1e30f;
     cudaEventRecord(e1, nullptr);
     if (cudaEventSynchronize(e1) != cudaSuccess) return 1e30f;
     float ms = 0.f;
     cudaEventElapsedTime(&ms, e0, e1);
-    if (ms * 0.25f < best) best = ms * 0.25f;
+    if (ms / (float)burst < best) best = ms / (float)burst;
   }
   return best;
 }
