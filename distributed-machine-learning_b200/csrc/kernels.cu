@@ -410,11 +410,20 @@ __global__ void __launch_bounds__(256) gap_kernel(const T* __restrict__ in, floa
 #pragma unroll
   for (int i = 0; i < V; ++i) acc[i] = 0.f;
   const T* base = in + (int64_t)img * hw * in_pitch + g * V;
-  for (int px = 0; px < hw; ++px) {
-    uint4 raw = *reinterpret_cast<const uint4*>(base + (int64_t)px * in_pitch);
-    const T* v = reinterpret_cast<const T*>(&raw);
+  // eight independent loads in flight per thread, summed in pixel order (same result as a plain loop: one thread's
+  // 49-64 dependent-latency loads were the whole cost of this kernel)
+  for (int px0 = 0; px0 < hw; px0 += 8) {
+    uint4 raw[8];
 #pragma unroll
-    for (int i = 0; i < V; ++i) acc[i] += to_f(v[i]);
+    for (int j = 0; j < 8; ++j)
+      if (px0 + j < hw) raw[j] = *reinterpret_cast<const uint4*>(base + (int64_t)(px0 + j) * in_pitch);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (px0 + j >= hw) break;
+      const T* v = reinterpret_cast<const T*>(&raw[j]);
+#pragma unroll
+      for (int i = 0; i < V; ++i) acc[i] += to_f(v[i]);
+    }
   }
   float inv = 1.f / (float)hw;
 #pragma unroll
