@@ -29,6 +29,10 @@ class DmlError(RuntimeError):
     pass
 
 
+class DmlCancelled(DmlError):
+    """dml_cancel stopped the call between two micro-batches (DML_ECANCELLED)."""
+
+
 def _stale() -> bool:
     if not os.path.exists(LIB_PATH):
         return True
@@ -69,6 +73,8 @@ _SIGS = {
     "dml_preprocess": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "dml_forward": [_vp, _i, _vp, _vp, _vp, _vp],
     "dml_infer": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp],
+    "dml_cancel": [_vp],
+    "dml_cancel_clear": [_vp],
     "dml_num_tensors": [_vp, C.POINTER(_i)],
     "dml_tensor_info": [_vp, _i, C.c_char_p, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_vp),
                         C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)],
@@ -111,6 +117,8 @@ def lib():
 
 
 def check(rc: int):
+    if rc == -5:
+        raise DmlCancelled(lib().dml_last_error().decode())
     if rc != 0:
         raise DmlError(f"dml error {rc}: {lib().dml_last_error().decode()}")
 

@@ -9,6 +9,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -81,6 +82,7 @@ struct dml_engine {
   bool weights_loaded = false;
   size_t off_lut = 0, off_input = 0, off_arena = 0, off_pooled = 0, off_logits = 0, off_tc = 0, ws_need = 0;
   int64_t launches = 0;
+  std::atomic<int> cancel{0};  // dml_cancel: checked between micro-batches
   dml::TcPlan tc;  // tensor maps etc. for the tcgen05 path
   bool s2d = false;          // K1 writes the space-to-depth input and the stem runs as a stride-1 halo conv (Net::S2d)
   size_t input_img_bytes = 0;
@@ -497,6 +499,7 @@ int dml_forward(dml_engine* e, int n, float* d_probs, int32_t* d_top5_idx, float
   CUDA_TRY(cudaSetDevice(e->device));
   cudaStream_t s = (cudaStream_t)stream;
   for (int i0 = 0; i0 < n; i0 += e->micro_batch) {
+    if (e->cancel.exchange(0)) return fail(DML_ECANCELLED, "cancelled before image %d of %d", i0, n);
     int cnt = n - i0 < e->micro_batch ? n - i0 : e->micro_batch;
     if (int rc = run_layers(e, i0, cnt, s)) return rc;
   }
@@ -513,11 +516,24 @@ int dml_infer(dml_engine* e, const uint8_t* d_pixels, const int64_t* d_img_off, 
   CUDA_TRY(cudaSetDevice(e->device));
   cudaStream_t s = (cudaStream_t)stream;
   for (int i0 = 0; i0 < n; i0 += e->micro_batch) {
+    if (e->cancel.exchange(0)) return fail(DML_ECANCELLED, "cancelled before image %d of %d", i0, n);
     int cnt = n - i0 < e->micro_batch ? n - i0 : e->micro_batch;
     if (int rc = run_pre(e, d_pixels, d_img_off, d_hw, d_xtab, d_ytab, i0, cnt, s)) return rc;
     if (int rc = run_layers(e, i0, cnt, s)) return rc;
   }
   return run_head(e, n, d_probs, d_top5_idx, d_top5_prob, s);
+}
+
+int dml_cancel(dml_engine* e) {
+  if (!e) return fail(DML_EINVAL, "engine is NULL");
+  e->cancel.store(1);
+  return 0;
+}
+
+int dml_cancel_clear(dml_engine* e) {
+  if (!e) return fail(DML_EINVAL, "engine is NULL");
+  e->cancel.store(0);
+  return 0;
 }
 
 int dml_num_tensors(dml_engine* e, int* n) {

@@ -716,7 +716,10 @@ void launch_fc(const float* pooled, const float* w, const float* b, float* logit
     return;
   }
   dim3 grid((unsigned)((n + FC_IMGS - 1) / FC_IMGS), (1000 + FC_COLS - 1) / FC_COLS);
+  // the activations buffer is reused for the per-warp partial sums [FC_WARPS][FC_IMGS][FC_COLS]: size it for both
   size_t smem = (size_t)FC_IMGS * cin * sizeof(float);
+  const size_t part = (size_t)FC_WARPS * FC_IMGS * FC_COLS * sizeof(float);
+  if (smem < part) smem = part;
   fc_kernel<<<grid, FC_WARPS * 32, smem, s>>>(pooled, w, b, logits, n, cin);
 }
 

@@ -338,15 +338,17 @@ int launch_stem_tc(const ConvParams& c, cudaStream_t s) {
     const uint32_t box[4] = {(uint32_t)c.cout, (uint32_t)TILE_W, (uint32_t)TILE_H, 1};
     if (tc_make_tiled_map(&map_o, c.out, 4, dims, strides, box, c.cout == 64 ? 128 : 64) != 0) return -1;
   }
-  static bool attr = false;
-  static int num_sms = 148;
-  if (!attr) {
+  // the opt-in shared-memory size is a per-device attribute: set it once on every device that launches the kernel
+  static bool attr[64] = {};
+  static int sms[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -1;
+  if (!attr[dev]) {
     if (cudaFuncSetAttribute(stem_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) return -1;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    attr = true;
+    if (cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms[dev] <= 0) sms[dev] = 148;
+    attr[dev] = true;
   }
+  const int num_sms = sms[dev];
   int per_sm = (int)((220 * 1024) / (smem + 1024));
   if (per_sm > 2) per_sm = 2;  // 416 threads per CTA
   if (per_sm < 1) per_sm = 1;

@@ -54,6 +54,9 @@ class Engine:
         # device-side inputs/outputs, sized for max_batch
         S = self.size
         self.max_pixels = max_batch * 300 * 300 * 3
+        # a single image above this is resized on the host through the same index tables (frontend.shrink_oversized)
+        self.max_image_bytes = max(S * S * 3, self.max_pixels // min(max_batch, 8))
+        self._host_slots = None
         self.d_pixels = torch.empty(self.max_pixels + 16, dtype=torch.uint8, device=dev)
         self.d_off = torch.empty(max_batch, dtype=torch.int64, device=dev)
         self.d_hw = torch.empty((max_batch, 2), dtype=torch.int32, device=dev)
@@ -215,12 +218,82 @@ class Engine:
         n = sl["n"]
         return sl["h_idx"][:n].numpy(), sl["h_prob"][:n].numpy()
 
+    def chunks(self, images):
+        """Splits a list of uint8 images into runs that fit one engine batch: at most max_batch images AND at most
+        the staging buffer's bytes (full-resolution pixels are uploaded, so the byte bound matters for anything larger
+        than the 300x300 pictures the reference bundles).  Oversized single images are shrunk on the host first."""
+        run, nbytes = [], 0
+        for im in images:
+            im = frontend.shrink_oversized(im, self.size, self.max_image_bytes)
+            if run and (len(run) == self.max_batch or nbytes + im.nbytes > self.max_pixels):
+                yield run
+                run, nbytes = [], 0
+            run.append(im)
+            nbytes += im.nbytes
+        if run:
+            yield run
+
+    def host_slot(self, k: int) -> dict:
+        """Pinned host arrays of slot k (two slots): frontend.HostBatch(..., into=slot) fills them in place, so
+        the H2D copies of submit() are asynchronous without a pin_memory() call per batch."""
+        torch = _torch()
+        if self._host_slots is None:
+            S, mb = self.size, self.max_batch
+            self._host_slots = []
+            for _ in range(2):
+                t = {"pixels": torch.empty(self.max_pixels + 16, dtype=torch.uint8).pin_memory(),
+                     "img_off": torch.empty(mb, dtype=torch.int64).pin_memory(),
+                     "hw": torch.empty((mb, 2), dtype=torch.int32).pin_memory(),
+                     "xtab": torch.empty((mb, S), dtype=torch.int32).pin_memory(),
+                     "ytab": torch.empty((mb, S), dtype=torch.int32).pin_memory()}
+                self._host_slots.append(({k2: v.numpy() for k2, v in t.items()}, t))
+        return self._host_slots[k][0]
+
+    def predict_pipelined(self, images, cancelled=None):
+        """uint8 HxWx3 arrays (any iterable, consumed lazily) -> (top5_idx [n,5], top5_prob [n,5]) through
+        submit()/collect(): while the GPU runs batch i, the caller's iterator (JPEG decoding) and the host-side
+        packing of batch i+1 proceed, and its H2D copy overlaps the kernels.  ``cancelled``: an optional
+        threading.Event checked between batches (the worker's task preemption, worker.py:944-953)."""
+        idx_out, prob_out = [], []
+        pending = None
+
+        def drain():
+            nonlocal pending
+            if pending is not None:
+                i, p = self.collect(pending)
+                idx_out.append(i.copy())
+                prob_out.append(p.copy())
+                pending = None
+
+        try:
+            for run in self.chunks(images):
+                if cancelled is not None and cancelled.is_set():
+                    raise _lib.DmlCancelled("cancelled between two batches")
+                hb = frontend.HostBatch(run, self.size, into=self.host_slot(self._submitted % 2))
+                t = self.submit(hb)
+                drain()
+                pending = t
+            drain()
+        except BaseException:
+            if pending is not None:  # leave no batch in flight behind an error
+                try:
+                    self.collect(pending)
+                except Exception:
+                    pass
+            raise
+        if not idx_out:
+            return np.zeros((0, 5), np.int32), np.zeros((0, 5), np.float32)
+        return np.concatenate(idx_out), np.concatenate(prob_out)
+
+    def cancel(self):
+        """Stops the dml_infer call in progress (or the next one) before its next micro-batch."""
+        _lib.check(self.l.dml_cancel(self.h))
+
     def predict_images(self, images, want_probs: bool = False):
         """uint8 HxWx3 arrays -> (top5_idx [n,5] int32, top5_prob [n,5] fp32[, probs [n,1000]])."""
         torch = _torch()
         idx_out, prob_out, probs_out = [], [], []
-        for i in range(0, len(images), self.max_batch):
-            chunk = images[i:i + self.max_batch]
+        for chunk in self.chunks(images):
             hb = frontend.HostBatch(chunk, self.size)
             self.upload(hb)
             self.infer_device(hb.n, want_probs)

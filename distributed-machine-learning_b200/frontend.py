@@ -48,32 +48,52 @@ def decode_file(path: str) -> np.ndarray:
         return decode_rgb(fh.read())
 
 
-class HostBatch:
-    """Concatenated uint8 pixels + per-image offsets, sizes and index tables."""
+def shrink_oversized(im: np.ndarray, size: int, max_bytes: int) -> np.ndarray:
+    """An image whose pixels would not fit the engine's staging buffer is resized on the host through the very
+    index tables the GPU kernel would use (rows first, then columns: a pure gather, so the result is the image
+    load_img(target_size=(size, size)) returns).  Anything smaller goes to the GPU untouched."""
+    if im.nbytes <= max_bytes:
+        return im
+    h, w = im.shape[:2]
+    return np.ascontiguousarray(im[nearest_table(h, size)][:, nearest_table(w, size)])
 
-    def __init__(self, images, size: int):
+
+class HostBatch:
+    """Concatenated uint8 pixels + per-image offsets, sizes and index tables.
+
+    ``into``: a dict of preallocated (ideally pinned) numpy arrays ``pixels`` / ``img_off`` / ``hw`` / ``xtab`` /
+    ``ytab`` to fill instead of allocating (the engine's reusable host slots)."""
+
+    def __init__(self, images, size: int, into: dict | None = None):
         n = len(images)
         self.n = n
         self.size = size
-        offs = np.zeros(n, dtype=np.int64)
-        hw = np.zeros((n, 2), dtype=np.int32)
-        xt = np.zeros((n, size), dtype=np.int32)
-        yt = np.zeros((n, size), dtype=np.int32)
-        total = 0
-        for i, im in enumerate(images):
+        for im in images:
             if im.ndim != 3 or im.shape[2] != 3 or im.dtype != np.uint8:
                 raise ValueError("images must be HxWx3 uint8")
+        sizes = np.fromiter((im.size for im in images), dtype=np.int64, count=n)
+        total = int(sizes.sum())
+        if into is None:
+            offs = np.zeros(n, dtype=np.int64)
+            hw = np.zeros((n, 2), dtype=np.int32)
+            xt = np.zeros((n, size), dtype=np.int32)
+            yt = np.zeros((n, size), dtype=np.int32)
+            pix = np.empty(total + 16, dtype=np.uint8)
+        else:
+            if n > into["img_off"].shape[0] or total + 16 > into["pixels"].size:
+                raise ValueError("batch does not fit the preallocated host buffers")
+            offs, hw, xt, yt = into["img_off"][:n], into["hw"][:n], into["xtab"][:n], into["ytab"][:n]
+            pix = into["pixels"][:total + 16]
+        if n:
+            offs[0] = 0
+            np.cumsum(sizes[:-1], out=offs[1:])
+            # one vectorised copy of all pixels (no per-image Python loop over the bytes)
+            np.concatenate([im.reshape(-1) for im in images], out=pix[:total])
+        ident = np.arange(size, dtype=np.int32)
+        for i, im in enumerate(images):
             h, w = im.shape[:2]
-            offs[i] = total
             hw[i] = (h, w)
             # load_img resizes only when (W, H) != (S, S); both tables are identity otherwise
-            if (w, h) == (size, size):
-                xt[i] = yt[i] = np.arange(size, dtype=np.int32)
-            else:
-                xt[i] = _table(w, size) if w != size else np.arange(size, dtype=np.int32)
-                yt[i] = _table(h, size) if h != size else np.arange(size, dtype=np.int32)
-            total += h * w * 3
-        pix = np.empty(total + 16, dtype=np.uint8)
-        for i, im in enumerate(images):
-            pix[offs[i]:offs[i] + im.size] = im.reshape(-1)
+            xt[i] = _table(w, size) if w != size else ident
+            yt[i] = _table(h, size) if h != size else ident
         self.pixels, self.img_off, self.hw, self.xtab, self.ytab = pix, offs, hw, xt, yt

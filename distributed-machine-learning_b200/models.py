@@ -23,6 +23,7 @@ from functools import partial
 import numpy as np
 
 from . import frontend
+from ._lib import DmlCancelled
 from .engine import Engine
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -46,6 +47,12 @@ def class_index():
         with open(path) as fh:
             raw = json.load(fh)
         _class_index = {int(k): (v[0], v[1]) for k, v in raw.items()}
+        missing = sum(1 for v in _class_index.values() if "?" in v[0])
+        if missing:
+            import warnings
+            warnings.warn(f"dml_b200: {missing} of {len(_class_index)} wnids in {path} are placeholders (Keras downloads "
+                          "imagenet_class_index.json from the network); set DML_B200_CLASS_INDEX to the real file",
+                          RuntimeWarning, stacklevel=2)
     return _class_index
 
 
@@ -80,13 +87,50 @@ def decode_top5(idx: np.ndarray, prob: np.ndarray):
     return [(ci[int(i)][0], ci[int(i)][1], np.float32(p)) for i, p in zip(idx, prob)]
 
 
-def _run(model_name: str, image_files: list, modelObj=None):
+class _Cancel:
+    """Hand-shake between a cancelled perform_inference coroutine and its worker thread."""
+
+    def __init__(self):
+        self.event = threading.Event()
+        self.lock = threading.Lock()
+        self.engine = None  # set while the thread owns the engine
+
+    def request(self):
+        with self.lock:
+            self.event.set()
+            if self.engine is not None:
+                self.engine.cancel()  # dml_cancel: the dml_infer in progress stops before its next micro-batch
+
+
+def _run(model_name: str, image_files: list, modelObj=None, cancel: _Cancel | None = None):
     eng = modelObj if isinstance(modelObj, Engine) else get_engine(model_name)
     files = list(image_files)
-    decoded = list(_pool().map(_decode_one, files))
-    good = [i for i, d in enumerate(decoded) if not isinstance(d, str)]
+    failed = {}
+    good = []
+
+    def decoded_images():
+        # the pool decodes ahead while the GPU works on the batches already handed over
+        for i, d in enumerate(_pool().map(_decode_one, files)):
+            if isinstance(d, str):
+                failed[i] = d
+            else:
+                good.append(i)
+                yield d
+
     with eng.lock:  # one engine is used by one thread at a time
-        idx, prob = eng.predict_images([decoded[i] for i in good])
+        if cancel is not None:
+            with cancel.lock:
+                if cancel.event.is_set():
+                    raise DmlCancelled("cancelled before the first batch")
+                cancel.engine = eng
+        try:
+            idx, prob = eng.predict_pipelined(decoded_images(), cancel.event if cancel is not None else None)
+        finally:
+            if cancel is not None:
+                with cancel.lock:
+                    cancel.engine = None
+                    if cancel.event.is_set():
+                        eng.l.dml_cancel_clear(eng.h)  # a flag raised after the last micro-batch must not hit the next task
     results = {}
     pos = {g: k for k, g in enumerate(good)}
     for i, f in enumerate(files):
@@ -95,23 +139,26 @@ def _run(model_name: str, image_files: list, modelObj=None):
             k = pos[i]
             results[key] = [decode_top5(idx[k], prob[k])]  # extra outer list: decode_predictions' batch dim
         else:
-            results[key] = decoded[i]
+            results[key] = failed[i]
     return results
 
 
-def run_inference_on_InceptionV3(image_files: list, modelObj=None):
+def run_inference_on_InceptionV3(image_files: list, modelObj=None, *, cancel=None):
     """models.py:23-46."""
-    return _run("InceptionV3", image_files, modelObj)
+    return _run("InceptionV3", image_files, modelObj, cancel)
 
 
-def run_inference_on_ResNet50(image_files: list, modelObj=None):
+def run_inference_on_ResNet50(image_files: list, modelObj=None, *, cancel=None):
     """models.py:48-71."""
-    return _run("ResNet50", image_files, modelObj)
+    return _run("ResNet50", image_files, modelObj, cancel)
 
 
 async def perform_inference(model_name, files):
     """models.py:74-91.  Stays a coroutine; the blocking decode + GPU call runs in
-    a worker thread (ctypes releases the GIL) instead of a fresh process pool."""
+    a worker thread (ctypes releases the GIL) instead of a fresh process pool.
+    Cancelling the awaiting task (the worker does that when a new WORKER_TASK_REQUEST
+    preempts the running one, worker.py:944-953) stops the thread at its next batch
+    boundary -- the reference's pool, by contrast, runs the cancelled task to the end."""
     if model_name == "InceptionV3":
         function = run_inference_on_InceptionV3
     elif model_name == "ResNet50":
@@ -119,7 +166,17 @@ async def perform_inference(model_name, files):
     else:
         return "Invalid model"
     loop = asyncio.get_running_loop()
-    return await loop.run_in_executor(None, partial(function, files))
+    cancel = _Cancel()
+    fut = loop.run_in_executor(None, partial(function, files, cancel=cancel))
+    try:
+        return await asyncio.shield(fut)
+    except asyncio.CancelledError:
+        cancel.request()
+        try:
+            await fut  # the thread leaves at its next batch boundary; nothing of this task is left running
+        except (DmlCancelled, asyncio.CancelledError):
+            pass
+        raise
 
 
 def perform_inference_without_async(model_name, files):
@@ -155,6 +212,24 @@ def dump_to_file(d, filename):
     with open(filename, "w") as fout:
         json_dumps_str = json.dumps(d, indent=4, cls=NpEncoder)
         print(json_dumps_str, file=fout)
+
+
+def merge_all_json_files(all_files, local_dir, output_file):
+    """The client's merge of a job's per-task result files into ``final_{jobid}.json``
+    (/root/reference/worker.py:1513-1534, called from get_output_cli :1617-1627): files that are missing from
+    ``local_dir`` are skipped, the dicts are merged with ``dict.update`` in list order (a later file wins on a
+    duplicate image name) and the result is written with dump_to_file.  ``local_dir`` is used as a plain string prefix,
+    as the reference does.  Returns the merged dict, or None when no file was there (nothing is written then)."""
+    available_files = [f for f in all_files if os.path.exists(local_dir + f)]
+    if len(available_files) == 0:
+        print("requested files are not available in provided directory")
+        return None
+    final_output: dict = {}
+    for f in available_files:
+        with open(local_dir + f, encoding="utf-8") as f1:
+            final_output.update(json.loads(f1.read()))
+    dump_to_file(final_output, local_dir + output_file)
+    return final_output
 
 
 class ModelParameters:

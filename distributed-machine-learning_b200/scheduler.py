@@ -19,6 +19,7 @@ Kept quirks, because they are the reference's behaviour:
 """
 from __future__ import annotations
 
+import json
 from dataclasses import dataclass, field
 
 from .models import ModelParameters
@@ -32,6 +33,35 @@ REFERENCE_COST = {
 }
 
 
+# The reference ships every task to its worker as ONE fixed-size datagram whose JSON payload field is
+# 2048 * 16 = 32768 bytes (struct "i255s6si32768s", /root/reference/packets.py:70-73).  pack() truncates a longer
+# payload silently, unpack() then fails in json.loads and returns None (:79-92): the task is dropped, never ACKed,
+# and its job never completes.  Each image costs its name plus its replica map {machine: [versions]}
+# (worker.py:289-297) -- about 265 bytes with 4 replicas -- so a WORKER_TASK_REQUEST holds ~120 images at most and
+# C3 batch sizes above that cannot travel through the real control plane, whatever the GPU could take.
+PACKET_JSON_BYTES = 2048 * 16
+
+
+def task_request_bytes(job_id, batch_id, model, images, replicas=None):
+    """Bytes of the JSON payload the leader would put into the WORKER_TASK_REQUEST for this chunk
+    (worker.py:297: {"jobid", "batchid", "model", "images": {name: {machine: [versions]}}}).
+    replicas: {image: {machine: [versions]}}; default = 4 replicas with one version each, named like the reference's
+    unique node names and versioned files."""
+    def default(image):
+        return {f"fa22-cs425-69{m:02d}.cs.illinois.edu:8000": [f"{image}_version1"] for m in (3, 4, 5, 6)}
+    payload = {"jobid": job_id, "batchid": batch_id, "model": model,
+               "images": {im: (replicas[im] if replicas is not None else default(im)) for im in images}}
+    return len(json.dumps(payload).encode())
+
+
+def max_images_per_task(sample_images, model="InceptionV3", replicas=None):
+    """Largest chunk of these image names whose task request still fits one datagram."""
+    n = 0
+    while n < len(sample_images) and task_request_bytes(10 ** 6, 10 ** 6, model, sample_images[:n + 1], replicas) <= PACKET_JSON_BYTES:
+        n += 1
+    return n
+
+
 @dataclass
 class Assignment:
     worker: str
@@ -40,6 +70,14 @@ class Assignment:
     batch_id: int
     images: list
     preempted: dict | None = None  # the chunk that was taken off this worker, if any
+
+    def wire_bytes(self, replicas=None) -> int:
+        return task_request_bytes(self.job_id, self.batch_id, self.model, self.images, replicas)
+
+    def fits_datagram(self, replicas=None) -> bool:
+        """False: the reference's Packet.pack would truncate this task request (packets.py:70-73) and the worker
+        would never see it."""
+        return self.wire_bytes(replicas) <= PACKET_JSON_BYTES
 
 
 @dataclass
@@ -68,8 +106,13 @@ class FairShareScheduler:
         self.cost[model].update(kw)
         self.model_dict[model].time = self._time(model, self.model_dict[model].batch_size)
 
-    def set_batch_size(self, model, batch_size, reference_quirk: bool = True):
-        """C3 / SET_BATCH_SIZE (worker.py:1028-1037)."""
+    def set_batch_size(self, model, batch_size, reference_quirk: bool = True, wire_cap: int | None = None):
+        """C3 / SET_BATCH_SIZE (worker.py:1028-1037).  The reference accepts any value; ``wire_cap`` (see
+        max_images_per_task) refuses one whose chunks (batch_size + 1 images with the off-by-one) would not fit a
+        WORKER_TASK_REQUEST datagram, instead of losing those tasks silently."""
+        if wire_cap is not None and int(batch_size) + (0 if self.fix_off_by_one else 1) > wire_cap:
+            raise ValueError(f"batch size {batch_size}: a task of {int(batch_size) + (0 if self.fix_off_by_one else 1)} images "
+                             f"does not fit the {PACKET_JSON_BYTES}-byte task datagram (at most {wire_cap} images)")
         st = self.model_dict[model]
         st.batch_size = int(batch_size)
         st.time = ModelParameters(batch_size=st.batch_size, **REFERENCE_COST["InceptionV3"]).execution_time_per_vm() \

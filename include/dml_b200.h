@@ -31,7 +31,8 @@ enum {
   DML_EINVAL = -1,   /* bad argument */
   DML_ESTATE = -2,   /* call order: workspace/weights not bound or loaded */
   DML_ECUDA = -3,    /* a CUDA runtime/driver call failed */
-  DML_ESIZE = -4     /* size beyond a stated limit */
+  DML_ESIZE = -4,    /* size beyond a stated limit */
+  DML_ECANCELLED = -5 /* dml_cancel was called: the call stopped between two micro-batches */
 };
 
 enum { DML_MODEL_RESNET50 = 0, DML_MODEL_INCEPTIONV3 = 1 };
@@ -112,6 +113,16 @@ int dml_forward(dml_engine* e, int n, float* d_probs, int32_t* d_top5_idx, float
 int dml_infer(dml_engine* e, const uint8_t* d_pixels, const int64_t* d_img_off, const int32_t* d_hw,
               const int32_t* d_xtab, const int32_t* d_ytab, int n, float* d_probs, int32_t* d_top5_idx,
               float* d_top5_prob, void* stream);
+
+/* Preemption: the reference's worker cancels the task it is running when a new
+ * WORKER_TASK_REQUEST arrives (worker.py:944-953).  dml_cancel may be called from
+ * any thread; the dml_infer / dml_forward call in progress on this engine (or the
+ * next one, if none is) stops before its next micro-batch and returns
+ * DML_ECANCELLED.  Kernels already enqueued still run; the outputs of a cancelled
+ * call are undefined.  The flag clears when it has been honoured, or through
+ * dml_cancel_clear. */
+int dml_cancel(dml_engine* e);
+int dml_cancel_clear(dml_engine* e);
 
 /* ---- inspection (parity taps, counters) ----------------------------------- */
 
