@@ -1984,6 +1984,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc5_kernel(const __grid_co
   }
 }
 
+#include "conv_chain.inc"
+
 }  // namespace
 
 // ------------------------------- host side ---------------------------------
@@ -2061,6 +2063,10 @@ int tc_init() {
   DML_V6_SHAPES_INIT(DML_V6_ATTR)
 #undef DML_V6_ATTR
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc6_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(conv_chain_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_chain_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc3_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc2x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
@@ -2731,6 +2737,155 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
   return 0;
 }
 
+
+// ---- conv_chain_kernel: plan + launch over explicit pointers ----
+bool chain_supported(const ChainArgs& a) {
+  if (a.h <= 0 || a.w <= 0 || a.w + 2 > 64) return false;
+  const int rpt = BLOCK_M / (a.w + 2);
+  const int rows = rpt * a.w;
+  if (rpt < 1 || a.h % (2 * rpt) != 0 || rows % 16 != 0 || rows > BLOCK_M) return false;
+  if (!a.y1 || !a.w3 || !a.b3 || !a.we || !a.be || !a.out) return false;
+  if ((a.res != nullptr) == (a.src2 != nullptr)) return false;   // exactly one of: residual tensor, second GEMM source
+  if ((a.wr != nullptr) != (a.y1n != nullptr) || (a.wr && !a.br)) return false;
+  if (a.src2 && !a.wr) return false;                              // variants built: res+next, src2+next, res only
+  if (a.y1_pitch % 8 || a.out_pitch % 8 || (a.res && a.res_pitch % 8) || (a.src2 && a.src2_pitch % 8) || (a.y1n && a.y1n_pitch % 8)) return false;
+  return true;
+}
+
+int chain_plan(ChainPlan* out, const ChainArgs& a, int n_capacity) {
+  if (!g_encode_tiled) return tc_fail("tc_init was not called");
+  if (!chain_supported(a)) return tc_fail("shape is not eligible for the bottleneck-tail chain kernel");
+  ChainPlan pl;
+  pl.wp = a.w + 2;
+  pl.rpt = BLOCK_M / pl.wp;
+  pl.rows = pl.rpt * a.w;
+  pl.ptiles_per_img = a.h / (2 * pl.rpt);
+  pl.box_bytes = (pl.rpt + 2) * pl.wp * 128;
+  const int reach = BLOCK_M + 2 * pl.wp + 2;  // rows the shifted views of a 128-row MMA may touch
+  const int box_rows = (pl.rpt + 2) * pl.wp;
+  pl.halo_bytes = ((box_rows > reach ? box_rows : reach) * 128 + 1023) / 1024 * 1024;
+  pl.kb2 = a.src2 ? 2 : 1;
+  pl.variant = a.src2 ? 1 : (a.wr ? 0 : 2);
+  const ChainSmem L = chain_smem(pl.rows, pl.halo_bytes, pl.kb2, a.res != nullptr, a.src2 != nullptr, a.wr != nullptr);
+  if (L.total > (uint32_t)SMEM_LIMIT) return tc_fail("chain kernel needs %u bytes of shared memory", L.total);
+  pl.smem = L.total;
+  pl.n_capacity = n_capacity;
+  const cuuint64_t M = (cuuint64_t)n_capacity * a.h * a.w;
+  CUresult r;
+  {  // halo of the 3x3: NHWC as (C, W, H, N), box {64, Wp, rpt + 2, 1}, zero fill outside the image
+    cuuint64_t gdim[4] = {(cuuint64_t)CH_C, (cuuint64_t)a.w, (cuuint64_t)a.h, (cuuint64_t)n_capacity};
+    cuuint64_t gstr[3] = {(cuuint64_t)a.y1_pitch * 2, (cuuint64_t)a.w * a.y1_pitch * 2, (cuuint64_t)a.h * a.w * a.y1_pitch * 2};
+    cuuint32_t box[4] = {(cuuint32_t)CH_C, (cuuint32_t)pl.wp, (cuuint32_t)(pl.rpt + 2), 1};
+    cuuint32_t es[4] = {1, 1, 1, 1};
+    r = g_encode_tiled(&pl.map_halo, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(a.y1), gdim, gstr, box, es,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return tc_fail("cuTensorMapEncodeTiled(chain halo) failed (%d)", (int)r);
+  }
+  auto weight_map = [&](CUtensorMap* m, const void* w, int k, int rows_total, int box_rows_) -> CUresult {
+    cuuint64_t d[2] = {(cuuint64_t)k, (cuuint64_t)rows_total};
+    cuuint64_t st[1] = {(cuuint64_t)k * 2};
+    cuuint32_t b[2] = {(cuuint32_t)CH_C, (cuuint32_t)box_rows_};
+    cuuint32_t es[2] = {1, 1};
+    return g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(w), d, st, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  };
+  if ((r = weight_map(&pl.map_w3, a.w3, 9 * CH_C, CH_C, 32)) != CUDA_SUCCESS) return tc_fail("chain: 3x3 weight map failed (%d)", (int)r);
+  if ((r = weight_map(&pl.map_we, a.we, pl.kb2 * CH_C, CH_N2, 128)) != CUDA_SUCCESS) return tc_fail("chain: expand weight map failed (%d)", (int)r);
+  pl.map_wr = pl.map_we;
+  if (a.wr && (r = weight_map(&pl.map_wr, a.wr, CH_N2, CH_C, 32)) != CUDA_SUCCESS) return tc_fail("chain: reduce weight map failed (%d)", (int)r);
+  auto pixel_map = [&](CUtensorMap* m, const void* base, int channels, int pitch, int box_rows_) -> CUresult {
+    cuuint64_t d[2] = {(cuuint64_t)channels, M};
+    cuuint64_t st[1] = {(cuuint64_t)pitch * 2};
+    cuuint32_t b[2] = {(cuuint32_t)CH_C, (cuuint32_t)box_rows_};
+    cuuint32_t es[2] = {1, 1};
+    return g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), d, st, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  };
+  if ((r = pixel_map(&pl.map_out, a.out, CH_N2, a.out_pitch, 16)) != CUDA_SUCCESS) return tc_fail("chain: output map failed (%d)", (int)r);
+  pl.map_res = pl.map_out; pl.map_s2 = pl.map_out;
+  if (a.res && (r = pixel_map(&pl.map_res, a.res, CH_N2, a.res_pitch, pl.rows)) != CUDA_SUCCESS) return tc_fail("chain: residual map failed (%d)", (int)r);
+  if (a.src2 && (r = pixel_map(&pl.map_s2, a.src2, CH_C, a.src2_pitch, pl.rows)) != CUDA_SUCCESS) return tc_fail("chain: second-source map failed (%d)", (int)r);
+  if (a.y1n && (a.y1n_pitch % 16 || reinterpret_cast<uintptr_t>(a.y1n) % 32)) return tc_fail("chain: next-reduce output must be 32-byte aligned per pixel");
+  pl.valid = true;
+  *out = pl;
+  return 0;
+}
+
+int launch_chain(const ChainPlan& pl, const ChainArgs& a, cudaStream_t s) {
+  if (!pl.valid) return tc_fail("chain plan is not valid");
+  if (a.n > pl.n_capacity) return tc_fail("batch of %d images exceeds the planned capacity", a.n);
+  ChainParams k{};
+  k.bias1 = a.b3; k.bias2 = a.be; k.bias3 = a.br;
+  k.y1n = reinterpret_cast<__nv_bfloat16*>(a.y1n); k.y1n_pitch = a.y1n_pitch;
+  k.out = reinterpret_cast<__nv_bfloat16*>(a.out); k.out_pitch = a.out_pitch;
+  k.n_img = a.n; k.ho = a.h; k.wo = a.w; k.wp = pl.wp; k.rpt = pl.rpt; k.ptiles_per_img = pl.ptiles_per_img; k.rows = pl.rows;
+  k.halo_bytes = pl.halo_bytes; k.box_bytes = pl.box_bytes; k.kb2 = pl.kb2; k.in_img0 = 0; k.pix_base = 0;
+  k.inv_wp = 1.0f / (float)pl.wp;
+  static const int ahead_env = getenv("DML_CHAIN_AHEAD") ? atoi(getenv("DML_CHAIN_AHEAD")) : 2;
+  k.ahead = ahead_env == 1 ? 1 : 2;
+  static const bool prof = getenv("DML_CHAIN_PROF") != nullptr;
+  k.prof = prof ? 1 : 0;
+  if (prof) {
+    static long long zero[160 * 40] = {};
+    cudaMemcpyToSymbol(g_chain_prof, zero, sizeof zero);
+  }
+  const int tiles = a.n * pl.ptiles_per_img;
+  const int pairs = g_num_sms / 2;
+  const int clusters = tiles < pairs ? tiles : pairs;
+  const dim3 grid(2 * clusters), block(CHAIN_THREADS);
+  static const bool dbg = getenv("DML_CHAIN_DEBUG") != nullptr;
+  static unsigned long long* h_word = nullptr;
+  if (dbg && !h_word) {
+    unsigned long long* d_word = nullptr;
+    if (cudaHostAlloc(&h_word, sizeof *h_word, cudaHostAllocMapped) == cudaSuccess && cudaHostGetDevicePointer(&d_word, h_word, 0) == cudaSuccess) {
+      *h_word = 0;
+      cudaMemcpyToSymbol(g_chain_dbg_ptr, &d_word, sizeof d_word);
+    }
+  }
+  if (pl.variant == 0)
+    launch_pdl(conv_chain_kernel<true, false, true>, grid, block, pl.smem, s, pl.map_halo, pl.map_w3, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k);
+  else if (pl.variant == 1)
+    launch_pdl(conv_chain_kernel<false, true, true>, grid, block, pl.smem, s, pl.map_halo, pl.map_w3, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k);
+  else
+    launch_pdl(conv_chain_kernel<true, false, false>, grid, block, pl.smem, s, pl.map_halo, pl.map_w3, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return tc_fail("conv_chain_kernel launch: %s", cudaGetErrorString(e));
+  if (prof) {
+    cudaStreamSynchronize(s);
+    static long long h[160 * 40];
+    cudaMemcpyFromSymbol(h, g_chain_prof, sizeof h);
+    double a[40] = {};
+    double nt = 0, loop = 0, ntl = 0;
+    for (int b = 0; b < 2 * clusters && b < 160; ++b) {
+      for (int i = 0; i < 38; ++i) a[i] += (double)h[b * 40 + i];
+      nt += (double)h[b * 40 + 39];
+      if (b % 2 == 0) { loop += (double)h[b * 40 + 38]; ntl += (double)h[b * 40 + 39]; }
+    }
+    if (nt < 1) nt = 1;
+    fprintf(stderr, "[chain prof] variant %d, %.1f tiles per cluster, %.0f cycles per tile | wait cycles per tile and CTA (one warp per role):", pl.variant,
+            ntl / clusters, loop / (ntl > 0 ? ntl : 1));
+    struct { const char* name; int first, count; } fam[] = {
+        {"producer:halo_empty", 3, 2}, {"producer|B:outc_empty", 19, 4}, {"producer|B:slot_free", 27, 4}, {"producer:s2_empty", 13, 2},
+        {"mma:halo_full", 1, 2}, {"mma:acc1_empty", 7, 2}, {"mma:acc2_empty", 33, 1}, {"mma:y2_full", 9, 1}, {"mma:s2_full", 11, 2},
+        {"mma:acc3_empty", 32, 1}, {"mma:outc_full", 15, 4}, {"A:acc1_full", 5, 2}, {"A:y2_free", 34, 1}, {"A:acc3_full", 31, 1},
+        {"B:acc2_full", 10, 1}, {"B:res_full", 23, 4}};
+    for (const auto& f : fam) {
+      double v = 0;
+      for (int i = 0; i < f.count; ++i) v += a[f.first + i];
+      if (v > 0) fprintf(stderr, " %s %.0f", f.name, v / nt);
+    }
+    fprintf(stderr, "\n");
+  }
+  if (dbg) {  // debugging aid: run to completion and report a wait that timed out (id, tile, block, warp)
+    cudaError_t se = cudaStreamSynchronize(s);
+    fprintf(stderr, "[chain debug] variant %d launch: sync -> %s, word %llx\n", pl.variant, cudaGetErrorString(se), h_word ? *h_word : 0ull);
+    if (h_word && *h_word)
+      fprintf(stderr, "[chain debug] variant %d: wait id %llu timed out at local tile %llu, block %llu, warp %llu (%s)\n", pl.variant,
+              *h_word & 0xff, (*h_word >> 8) & 0xffff, (*h_word >> 24) & 0xffff, (*h_word >> 40) & 0xff, cudaGetErrorString(se));
+  }
+  return 0;
+}
+
 namespace {
 // milliseconds of one launch, or a huge number if the candidate cannot run: one warm-up, then the best of
 // three bursts of four launches (the first bursts after an idle period run at ramping clocks)
@@ -2752,6 +2907,27 @@ float time_plan(const TcOpPlan& op, const ConvParams& p, cudaEvent_t e0, cudaEve
   return best;
 }
 }  // namespace
+
+// ChainArgs of the chain led by op `lead` over the engine's tensors (ptr(tensor id) -> device pointer of the view)
+template <typename PtrFn>
+static void chain_args(const Net& net, uint8_t* wts, int lead, int n, PtrFn ptr, ChainArgs* a) {
+  const Op& o3 = net.ops[lead];
+  const Op& oe = net.ops[o3.chain_exp];
+  const Tensor& ty1 = net.tensors[o3.in];
+  const Tensor& tout = net.tensors[oe.out];
+  a->y1 = ptr(o3.in); a->y1_pitch = ty1.c_pitch;
+  a->w3 = wts + o3.wpack_off; a->b3 = reinterpret_cast<const float*>(wts + o3.bias_off);
+  a->we = wts + oe.wpack_off; a->be = reinterpret_cast<const float*>(wts + oe.bias_off);
+  if (oe.res >= 0) { a->res = ptr(oe.res); a->res_pitch = net.tensors[oe.res].c_pitch; }
+  if (oe.in2 >= 0) { a->src2 = ptr(oe.in2); a->src2_pitch = net.tensors[oe.in2].c_pitch; }
+  a->out = ptr(oe.out); a->out_pitch = tout.c_pitch;
+  if (o3.chain_red >= 0) {
+    const Op& orr = net.ops[o3.chain_red];
+    a->wr = wts + orr.wpack_off; a->br = reinterpret_cast<const float*>(wts + orr.bias_off);
+    a->y1n = ptr(orr.out); a->y1n_pitch = net.tensors[orr.out].c_pitch;
+  }
+  a->n = n; a->h = ty1.h; a->w = ty1.w;
+}
 
 int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t off_input, size_t off_tc, uint8_t* wts,
             int micro_batch, int max_batch) {
@@ -2842,9 +3018,58 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
         if (ms < best * 0.98f) { best = ms; plan->ops[i] = cand; }
       }
     }
+    plan->ops[i].best_ms = best;
     if (tune_log)
       fprintf(stderr, "[tune] %s -> v%d bn %d group %d stages %d: %.4f ms (heuristic %.4f)\n", op.name.c_str(), plan->ops[i].version,
               plan->ops[i].bn, plan->ops[i].group, plan->ops[i].stages, best, first);
+  }
+  // ---- bottleneck-tail chains (conv_chain.inc): fused kernel against the three separate ones ----
+  plan->chains.assign(net.ops.size(), ChainPlan());
+  plan->chained.assign(net.ops.size(), 0);
+  if (!getenv("DML_NO_CHAIN")) {
+    auto tptr = [&](int t) -> uint8_t* {
+      const Tensor& tt = net.tensors[t];
+      return ws + off_arena + ((size_t)net.bufs[tt.buf].offset * micro_batch + tt.c_off) * 2;
+    };
+    for (size_t i = 0; i < net.ops.size(); ++i) {
+      const Op& o3 = net.ops[i];
+      if (o3.chain_exp < 0) continue;
+      const Op& oe = net.ops[o3.chain_exp];
+      const Tensor& ty1 = net.tensors[o3.in];
+      if (ty1.buf < 0 || !plan->ops[i].valid || !plan->ops[o3.chain_exp].valid) continue;
+      ChainArgs a;
+      chain_args(net, wts, (int)i, micro_batch, tptr, &a);
+      ChainPlan cp;
+      if (chain_plan(&cp, a, micro_batch) != 0) {
+        if (tune_log) fprintf(stderr, "[tune] chain at %s not planned: %s\n", o3.name.c_str(), tc_last_error());
+        continue;
+      }
+      bool use = true;
+      if (autotune) {
+        float best = 1e30f;
+        if (launch_chain(cp, a, nullptr) != 0 || cudaDeviceSynchronize() != cudaSuccess) return tc_fail("chain kernel failed at %s: %s", o3.name.c_str(), cudaGetErrorString(cudaGetLastError()));
+        for (int rep = 0; rep < 3; ++rep) {
+          cudaEventRecord(ev0, nullptr);
+          for (int k = 0; k < 4; ++k) launch_chain(cp, a, nullptr);
+          cudaEventRecord(ev1, nullptr);
+          if (cudaEventSynchronize(ev1) != cudaSuccess) return tc_fail("chain kernel failed at %s: %s", o3.name.c_str(), cudaGetErrorString(cudaGetLastError()));
+          float ms = 0.f;
+          cudaEventElapsedTime(&ms, ev0, ev1);
+          if (ms / 4.f < best) best = ms / 4.f;
+        }
+        cp.ms = best;
+        cp.ms_separate = plan->ops[i].best_ms + plan->ops[o3.chain_exp].best_ms + (o3.chain_red >= 0 ? plan->ops[o3.chain_red].best_ms : 0.f);
+        use = cp.ms < cp.ms_separate || getenv("DML_FORCE_CHAIN");
+        if (tune_log)
+          fprintf(stderr, "[tune] chain %s + %s%s%s: fused %.4f ms, separate %.4f ms -> %s\n", o3.name.c_str(), oe.name.c_str(),
+                  o3.chain_red >= 0 ? " + " : "", o3.chain_red >= 0 ? net.ops[o3.chain_red].name.c_str() : "", cp.ms, cp.ms_separate,
+                  use ? "fused" : "separate");
+      }
+      if (!use) continue;
+      plan->chains[i] = cp;
+      plan->chained[o3.chain_exp] = 1;
+      if (o3.chain_red >= 0) plan->chained[o3.chain_red] = 1;
+    }
   }
   if (autotune) {
     cudaEventDestroy(ev0);
@@ -2852,6 +3077,17 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     if (cudaDeviceSynchronize() != cudaSuccess) return tc_fail("autotune: %s", cudaGetErrorString(cudaGetLastError()));
   }
   return 0;
+}
+
+int launch_chain_tc(const TcPlan& plan, const Net& net, uint8_t* wts, int lead, int n, uint8_t* ws, size_t off_arena, cudaStream_t s) {
+  if (lead < 0 || lead >= (int)plan.chains.size() || !plan.chains[lead].valid) return tc_fail("no chain plan for op %d", lead);
+  auto tptr = [&](int t) -> uint8_t* {
+    const Tensor& tt = net.tensors[t];
+    return ws + off_arena + ((size_t)net.bufs[tt.buf].offset * plan.micro_batch + tt.c_off) * 2;
+  };
+  ChainArgs a;
+  chain_args(net, wts, lead, n, tptr, &a);
+  return launch_chain(plan.chains[lead], a, s);
 }
 
 int launch_conv_tc(const TcPlan& plan, int op_index, const ConvParams& p, int img0, cudaStream_t s, int* nlaunch) {

@@ -37,10 +37,39 @@ struct TcOpPlan {
   int wp = 0, rows_box = 0, tiles_per_img = 0, q_valid = 0, a_stage_bytes = 0, a_stages = 0, b_stages = 0;
   // v6 (halo kernel, resident filter)
   int a_cb_bytes = 0, row_bytes = 0;
+  float best_ms = 0.f;  // autotune: time of the chosen plan
 };
+
+// The tail of a ResNet50 conv2 bottleneck as one kernel (conv_chain.inc): 3x3 -> 1x1 expand (+ residual, or + the folded
+// projection shortcut as a second GEMM source) -> the next block's 1x1 reduce.
+struct ChainArgs {
+  const void* y1 = nullptr; int y1_pitch = 0;      // input of the 3x3: [n][h][w][64] bf16 (pitch in elements)
+  const void* w3 = nullptr; const float* b3 = nullptr;   // packed [64][9][64], folded bias
+  const void* we = nullptr; const float* be = nullptr;   // packed [256][64 (+ 64 of the projection)], folded bias (sum)
+  const void* res = nullptr; int res_pitch = 0;    // residual [n*h*w][256], or nullptr
+  const void* src2 = nullptr; int src2_pitch = 0;  // second GEMM source [n*h*w][64] (projection input), or nullptr
+  void* out = nullptr; int out_pitch = 0;          // block output [n*h*w][256]
+  const void* wr = nullptr; const float* br = nullptr;   // next block's reduce: packed [64][256], folded bias; or nullptr
+  void* y1n = nullptr; int y1n_pitch = 0;          // its output [n*h*w][64]
+  int n = 0, h = 0, w = 0;
+};
+struct ChainPlan {
+  bool valid = false;
+  alignas(64) CUtensorMap map_halo, map_w3, map_we, map_wr, map_res, map_out, map_s2;
+  int variant = 0;  // 0: residual + next reduce, 1: second source + next reduce, 2: residual, no next reduce
+  int wp = 0, rpt = 0, rows = 0, ptiles_per_img = 0, box_bytes = 0, halo_bytes = 0, kb2 = 1;
+  size_t smem = 0;
+  int n_capacity = 0;
+  float ms = 0.f, ms_separate = 0.f;  // autotune: this kernel against the three separate ones
+};
+bool chain_supported(const ChainArgs& a);
+int chain_plan(ChainPlan* out, const ChainArgs& a, int n_capacity);
+int launch_chain(const ChainPlan& plan, const ChainArgs& a, cudaStream_t s);
 
 struct TcPlan {
   std::vector<TcOpPlan> ops;  // indexed like Net::ops
+  std::vector<ChainPlan> chains;  // indexed like Net::ops; valid at the 3x3 that leads a chain the engine runs fused
+  std::vector<char> chained;      // op is computed inside a valid chain's launch
   int micro_batch = 0;
 };
 
@@ -62,6 +91,8 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
 int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune& tune);
 int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s);
 int launch_conv_tc(const TcPlan& plan, int op_index, const ConvParams& p, int img0, cudaStream_t s, int* nlaunch);
+// Runs the fused chain led by op `lead` (plan.chains[lead].valid) over the first n images of the arena.
+int launch_chain_tc(const TcPlan& plan, const Net& net, uint8_t* wts, int lead, int n, uint8_t* ws, size_t off_arena, cudaStream_t s);
 const char* tc_last_error();
 // Tiled bf16 tensor map (rank <= 5) for kernels outside conv_tc.cu; swizzle_bytes in {0, 32, 64, 128}.
 int tc_make_tiled_map(CUtensorMap* out, void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,

@@ -154,6 +154,7 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
   for (size_t oi = 0; oi < net.ops.size(); ++oi) {
     const dml::Op& op = net.ops[oi];
     if (op.skip) continue;  // computed by its leader (Op::merge_with)
+    if (e->use_tc && oi < e->tc.chained.size() && e->tc.chained[oi]) continue;  // computed inside its chain's launch
     const int out_t = op.merged_out >= 0 ? op.merged_out : op.out;
     const int cout_x = op.merged_cout > 0 ? op.merged_cout : op.cout;
     const dml::Tensor& ti = net.tensors[op.in];
@@ -177,7 +178,12 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
         p.hi2 = t2.h; p.wi2 = t2.w; p.cin2 = op.cin2; p.in2_pitch = t2.c_pitch; p.stride2 = op.stride2; p.cin2_pad = op.cin2_pad;
       }
       int nl = 0;
-      if (e->s2d && (int)oi == net.s2d.op) {
+      if (e->use_tc && oi < e->tc.chains.size() && e->tc.chains[oi].valid) {
+        // 3x3 + expand (+ residual / folded shortcut) + the next block's reduce as one kernel
+        if (dml::launch_chain_tc(e->tc, net, e->wts, (int)oi, cnt, e->ws, e->off_arena, s) != 0)
+          return fail(DML_ECUDA, "chain kernel launch failed at %s: %s", op.name.c_str(), dml::tc_last_error());
+        nl = 1;
+      } else if (e->s2d && (int)oi == net.s2d.op) {
         dml::ConvParams p2 = stem_s2d_params(e, img0, cnt);
         if (dml::launch_conv_tc_plan(e->stem_plan, p2, s) != 0)
           return fail(DML_ECUDA, "stem conv launch failed for %s: %s", op.name.c_str(), dml::tc_last_error());
@@ -607,7 +613,8 @@ int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* 
     const dml::Tensor& to = net.tensors[op.merged_out >= 0 ? op.merged_out : op.out];
     const int cout_x = op.merged_cout > 0 ? op.merged_cout : op.cout;
     nm = op.name; k = (int)op.kind;
-    if (op.skip) {  // a follower of a merged 1x1 pair: its work is reported by the leader
+    const bool chained = e->use_tc && (size_t)i < e->tc.chained.size() && e->tc.chained[i];
+    if (op.skip || chained) {  // a follower of a merged 1x1 pair / a member of a fused chain: reported by its leader
       if (name && name_cap > 0) snprintf(name, name_cap, "%s", nm.c_str());
       if (kind) *kind = k;
       if (impl) *impl = e->use_tc ? 1 : 0;
@@ -627,6 +634,21 @@ int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* 
         ab += (int64_t)((t2.h + op.stride2 - 1) / op.stride2) * ((t2.w + op.stride2 - 1) / op.stride2) * t2.c * e->act_bytes;
       }
       im = (e->use_tc && (dml::tc_supported(op) || (op.cin == 3 && op.stride == 2))) ? 1 : 0;
+      if (e->use_tc && (size_t)i < e->tc.chains.size() && e->tc.chains[i].valid) {
+        // fused chain: this launch also does the expand (+ shortcut) and the next reduce; y2 and the re-read of `out` never reach HBM
+        const dml::Op& oe = net.ops[op.chain_exp];
+        const dml::Tensor& te = net.tensors[oe.out];
+        const int64_t px = (int64_t)te.h * te.w;
+        macs += px * oe.cout * (oe.cin + oe.cin2);
+        wb += (int64_t)oe.cout * (oe.cin + oe.cin2) * 2 + oe.cout * 4;
+        ab = in_b + px * oe.cout * 2 /*out*/ + (oe.res >= 0 ? px * oe.cout * 2 : px * oe.cin2 * 2) /*residual or second source*/;
+        if (op.chain_red >= 0) {
+          const dml::Op& orr = net.ops[op.chain_red];
+          macs += px * orr.cout * orr.cin;
+          wb += (int64_t)orr.cout * orr.cin * 2 + orr.cout * 4;
+          ab += px * orr.cout * 2;
+        }
+      }
     }
   }
   if (name && name_cap > 0) snprintf(name, name_cap, "%s", nm.c_str());
@@ -706,6 +728,25 @@ int dml_conv2d_bf16(int impl, const void* d_in, const void* d_w, const float* d_
   tune.bn = tile_n; tune.stages = stages & 0xff; tune.group = (stages >> 8) & 0xff; tune.res_direct = (stages >> 16) & 3; tune.version = impl == 4 ? 3 : (impl == 5 ? 4 : (impl == 6 ? 5 : (impl == 7 ? 6 : (impl == 8 ? 7 : impl))));  // 5 = CTA-pair kernel, 6 = weights-as-A kernel, 7 = resident-filter halo kernel, 8 = the same on CTA pairs
   if (dml::tc_plan_one(&plan, p, n, tune) != 0) return fail(DML_EINVAL, "%s", dml::tc_last_error());
   if (dml::launch_conv_tc_plan(plan, p, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
+  return 0;
+}
+
+int dml_chain_bf16(const void* d_y1, const void* d_w3, const float* d_b3, const void* d_we, const float* d_be,
+                   const void* d_res, const void* d_src2, void* d_out, const void* d_wr, const float* d_br, void* d_y1n,
+                   int n, int h, int w, void* stream) {
+  if (n < 1) return fail(DML_EINVAL, "n must be positive");
+  if (dml::tc_init() != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
+  dml::ChainArgs a;
+  a.y1 = d_y1; a.y1_pitch = 64;
+  a.w3 = d_w3; a.b3 = d_b3; a.we = d_we; a.be = d_be;
+  a.res = d_res; a.res_pitch = 256;
+  a.src2 = d_src2; a.src2_pitch = 64;
+  a.out = d_out; a.out_pitch = 256;
+  a.wr = d_wr; a.br = d_br; a.y1n = d_y1n; a.y1n_pitch = 64;
+  a.n = n; a.h = h; a.w = w;
+  dml::ChainPlan plan;
+  if (dml::chain_plan(&plan, a, n) != 0) return fail(DML_EINVAL, "%s", dml::tc_last_error());
+  if (dml::launch_chain(plan, a, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
   return 0;
 }
 

@@ -262,6 +262,39 @@ void build_resnet50(Builder& b) {
       net->tensors[x].name = n + "_out";
     }
   }
+  if (b.fuse_shortcut) {
+    // conv2: every block's (3x3, expand) and the following block's reduce form a chain the engine may run as one kernel
+    for (int oi = 0; oi + 1 < (int)net->ops.size(); ++oi) {
+      Op& o3 = net->ops[oi];
+      Op& oe = net->ops[oi + 1];
+      if (o3.kind != OP_CONV || o3.kh != 3 || o3.kw != 3 || o3.stride != 1 || o3.cin != 64 || o3.cout != 64) continue;
+      if (oe.kind != OP_CONV || oe.kh != 1 || oe.in != o3.out || oe.cin != 64 || oe.cout != 256 || !oe.relu) continue;
+      if (!((oe.res >= 0) != (oe.in2 >= 0)) || (oe.in2 >= 0 && (oe.stride2 != 1 || oe.cin2 != 64))) continue;
+      o3.chain_exp = oi + 1;
+      oe.chain_lead = oi;
+      int last = oi + 1;
+      if (oi + 2 < (int)net->ops.size()) {
+        Op& orr = net->ops[oi + 2];
+        if (orr.kind == OP_CONV && orr.kh == 1 && orr.kw == 1 && orr.stride == 1 && orr.in == oe.out && orr.cin == 256 && orr.cout == 64 &&
+            orr.relu && orr.res < 0 && orr.in2 < 0) {
+          o3.chain_red = oi + 2;
+          orr.chain_lead = oi;
+          last = oi + 2;
+        }
+      }
+      if (oe.in2 >= 0 && o3.chain_red < 0) {  // the fused kernel has no (second source, no next reduce) variant
+        o3.chain_exp = -1; oe.chain_lead = -1;
+        continue;
+      }
+      // the fused kernel reads and writes every tensor of the chain during ONE launch: all of them are live from the
+      // lead to the last member
+      for (int k = oi; k <= last; ++k) {
+        const Op& m = net->ops[k];
+        for (int t : {m.in, m.out, m.res, m.in2})
+          if (t >= 0) { b.touch(t, oi); b.touch(t, last); }
+      }
+    }
+  }
   b.head(x);
 }
 

@@ -58,6 +58,10 @@ struct Op {
   int merged_cout = 0, merged_out = -1;  // leader: summed Cout and the tensor that holds all slices
   int merge_row0 = 0;                    // leader and followers: first row of this op inside the merged weight / bias block
   int64_t merged_w_off = 0, merged_b_off = 0;  // leader: start of the merged block (bytes into the weights buffer)
+  // Bottleneck-tail chain (ResNet50 conv2, conv_chain.inc): the 3x3 (the chain's lead) may run fused with the block's
+  // 1x1 expand (chain_exp) and the next block's 1x1 reduce (chain_red, -1 for the stage's last block); chain_lead on
+  // the members points back.  The engine decides at plan time whether the fused kernel or the separate ones run.
+  int chain_exp = -1, chain_red = -1, chain_lead = -1;
   int in2 = -1, cin2 = 0, cin2_pad = 0, stride2 = 1;
   int w2_kernel = -1, w2_bias = -1, w2_gamma = -1, w2_beta = -1, w2_mean = -1, w2_var = -1;
   float eps2 = 0.f;

@@ -181,6 +181,18 @@ int dml_conv2d_bf16(int impl, const void* d_in, const void* d_w, const float* d_
                     int kw, int stride, int pad_h, int pad_w, int cin_pad, int relu, int tile_n, int stages,
                     void* stream);
 
+/* The tail of a ResNet50 conv2 bottleneck block of predict (models.py:65; Keras block1: _2_conv 3x3 -> _3_conv 1x1
+ * -> Add -> ReLU, then the next block's _1_conv) as ONE kernel over explicit device buffers, all bf16 NHWC with
+ * contiguous channels: y1 [n][h][w][64] -> y2 = relu(conv3x3(y1) + b3) (never stored) -> out [n][h][w][256] =
+ * relu(We y2 (+ Wp src2) + be (+ res)) -> y1n [n][h][w][64] = relu(Wr out + br).  Exactly one of d_res ([n][h][w][256])
+ * and d_src2 ([n][h][w][64], the projection shortcut's input; We then holds [256][64 + 64]) is given; d_wr / d_br /
+ * d_y1n may all be NULL (no next reduce; only with d_res).  Weights packed as for dml_conv2d_bf16.  Needs w <= 62,
+ * h a multiple of 2 * floor(128 / (w + 2)) and floor(128 / (w + 2)) * w a multiple of 16 (56 x 56 qualifies).
+ * Results are bit-identical to the three dml_conv2d_bf16 calls it replaces.  The unit-test hook of that kernel. */
+int dml_chain_bf16(const void* d_y1, const void* d_w3, const float* d_b3, const void* d_we, const float* d_be,
+                   const void* d_res, const void* d_src2, void* d_out, const void* d_wr, const float* d_br, void* d_y1n,
+                   int n, int h, int w, void* stream);
+
 /* The dense(1000) + softmax + top-5 head with NO device allocation anywhere: no
  * engine, no workspace.  (No counterpart in the reference: its Keras model owns
  * all of its memory.)  It is for callers that cannot allocate device memory --
