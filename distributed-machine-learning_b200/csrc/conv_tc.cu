@@ -22,7 +22,14 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <chrono>
+#include <fstream>
+#include <map>
+#include <sstream>
 #include <string>
+#include <dlfcn.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 namespace dml {
 namespace {
@@ -2908,6 +2915,72 @@ float time_plan(const TcOpPlan& op, const ConvParams& p, cudaEvent_t e0, cudaEve
 }
 }  // namespace
 
+// ---- autotune results: remembered per (library, model, micro-batch, SM count) ----
+// The table chosen by timing is kept in the process (a second engine of the same shape plans without timing anything, and gets
+// the same kernels) and in a small text file (DML_TUNE_CACHE_DIR, default .tune_cache/ next to the library; DML_TUNE_CACHE=0 turns the file
+// off), so that later processes on the same machine -- the ranks of a job, the next run -- start with it.  Timing itself is
+// bounded by DML_TUNE_BUDGET_MS of wall time (default 30000): ops past the budget keep the heuristic plan.
+struct TuneChoice {
+  int version = 0, bn = 0, group = 0, res_direct = 0, chain = -1;  // chain: -1 not a chain lead, 0 separate, 1 fused
+  float ms = 0.f;
+};
+static std::map<std::string, std::vector<TuneChoice>> g_tune_cache;
+
+static std::string tune_key(const Net& net, int micro_batch) {
+  char buf[160];
+  snprintf(buf, sizeof buf, "v3_m%d_mb%d_ops%zu_sm%d_w%lld", net.model, micro_batch, net.ops.size(), g_num_sms, (long long)net.weights_bytes);
+  return buf;
+}
+static std::string tune_file(const std::string& key) {
+  const char* off = getenv("DML_TUNE_CACHE");
+  if (off && off[0] == '0') return "";
+  std::string dir;
+  if (const char* d = getenv("DML_TUNE_CACHE_DIR")) {
+    dir = d;
+  } else {  // next to the library itself
+    Dl_info info;
+    if (!dladdr(reinterpret_cast<const void*>(&tune_key), &info) || !info.dli_fname) return "";
+    const std::string lib = info.dli_fname;
+    const size_t slash = lib.find_last_of('/');
+    dir = (slash == std::string::npos ? std::string(".") : lib.substr(0, slash)) + "/.tune_cache";
+  }
+  mkdir(dir.c_str(), 0755);
+  return dir + "/tune_" + key + ".txt";
+}
+static bool tune_load(const std::string& key, size_t nops, std::vector<TuneChoice>* out) {
+  auto it = g_tune_cache.find(key);
+  if (it != g_tune_cache.end() && it->second.size() == nops) { *out = it->second; return true; }
+  const std::string fn = tune_file(key);
+  if (fn.empty()) return false;
+  std::ifstream f(fn);
+  if (!f) return false;
+  std::vector<TuneChoice> v(nops);
+  size_t n = 0, idx;
+  TuneChoice c;
+  while (f >> idx >> c.version >> c.bn >> c.group >> c.res_direct >> c.chain >> c.ms) {
+    if (idx >= nops) return false;
+    v[idx] = c;
+    ++n;
+  }
+  if (n != nops) return false;
+  g_tune_cache[key] = v;
+  *out = v;
+  return true;
+}
+static void tune_store(const std::string& key, const std::vector<TuneChoice>& v) {
+  g_tune_cache[key] = v;
+  const std::string fn = tune_file(key);
+  if (fn.empty()) return;
+  const std::string tmp = fn + "." + std::to_string((long long)getpid()) + ".tmp";
+  {
+    std::ofstream f(tmp);
+    if (!f) return;
+    for (size_t i = 0; i < v.size(); ++i)
+      f << i << ' ' << v[i].version << ' ' << v[i].bn << ' ' << v[i].group << ' ' << v[i].res_direct << ' ' << v[i].chain << ' ' << v[i].ms << '\n';
+  }
+  rename(tmp.c_str(), fn.c_str());  // atomic: concurrent ranks write the same table
+}
+
 // ChainArgs of the chain led by op `lead` over the engine's tensors (ptr(tensor id) -> device pointer of the view)
 template <typename PtrFn>
 static void chain_args(const Net& net, uint8_t* wts, int lead, int n, PtrFn ptr, ChainArgs* a) {
@@ -2940,6 +3013,13 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   if (autotune && (cudaEventCreate(&ev0) != cudaSuccess || cudaEventCreate(&ev1) != cudaSuccess))
     return tc_fail("autotune: cudaEventCreate failed");
+  const std::string key = tune_key(net, micro_batch);
+  std::vector<TuneChoice> cached, chosen(net.ops.size());
+  const bool have_cache = autotune && !getenv("DML_TUNE_FRESH") && tune_load(key, net.ops.size(), &cached);
+  if (tune_log && have_cache) fprintf(stderr, "[tune] using the remembered table %s\n", key.c_str());
+  const double budget_ms = getenv("DML_TUNE_BUDGET_MS") ? atof(getenv("DML_TUNE_BUDGET_MS")) : 30000.0;
+  const auto tune_t0 = std::chrono::steady_clock::now();
+  bool over_budget = false;
   for (size_t i = 0; i < net.ops.size(); ++i) {
     const Op& op = net.ops[i];
     if (!tc_supported(op) || op.skip) continue;  // a follower of a merged 1x1 pair is computed by its leader
@@ -2968,8 +3048,22 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
       p.in2 = ws + off_arena + ((size_t)net.bufs[t2.buf].offset * micro_batch + t2.c_off) * 2;
       p.hi2 = t2.h; p.wi2 = t2.w; p.cin2 = op.cin2; p.in2_pitch = t2.c_pitch; p.stride2 = op.stride2; p.cin2_pad = op.cin2_pad;
     }
+    if (have_cache && cached[i].version != 0) {
+      TcTune t;
+      t.version = cached[i].version; t.bn = cached[i].bn; t.group = cached[i].group; t.res_direct = cached[i].res_direct;
+      if (tc_plan_one(&plan->ops[i], p, micro_batch, t) == 0 && plan->ops[i].version == cached[i].version && plan->ops[i].bn == cached[i].bn) {
+        plan->ops[i].best_ms = cached[i].ms;
+        chosen[i] = cached[i];
+        continue;
+      }
+    }
     if (tc_plan_one(&plan->ops[i], p, micro_batch, TcTune()) != 0) return -1;
     if (!autotune) continue;
+    if (!over_budget && std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tune_t0).count() > budget_ms) {
+      over_budget = true;
+      if (tune_log) fprintf(stderr, "[tune] time budget of %.0f ms used up at %s: the remaining layers keep the heuristic plan\n", budget_ms, op.name.c_str());
+    }
+    if (over_budget) continue;
     // Time the candidate kernels / N tiles on the real buffers (contents do not matter) and keep the
     // fastest.  Every candidate produces bit-identical results (tests/test_gpu_kernels.py).
     if (!warmed) {  // bring the clocks up before the first comparison (~20 ms of launches)
@@ -3019,6 +3113,8 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
       }
     }
     plan->ops[i].best_ms = best;
+    chosen[i].version = plan->ops[i].version; chosen[i].bn = plan->ops[i].bn; chosen[i].group = plan->ops[i].group;
+    chosen[i].res_direct = plan->ops[i].has_res ? (plan->ops[i].res_direct ? 2 : 1) : 0; chosen[i].ms = best;
     if (tune_log)
       fprintf(stderr, "[tune] %s -> v%d bn %d group %d stages %d: %.4f ms (heuristic %.4f)\n", op.name.c_str(), plan->ops[i].version,
               plan->ops[i].bn, plan->ops[i].group, plan->ops[i].stages, best, first);
@@ -3045,7 +3141,10 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
         continue;
       }
       bool use = true;
-      if (autotune) {
+      if (have_cache && cached[i].chain >= 0) {
+        use = cached[i].chain == 1;
+        chosen[i].chain = cached[i].chain;
+      } else if (autotune && !over_budget) {
         float best = 1e30f;
         if (launch_chain(cp, a, nullptr) != 0 || cudaDeviceSynchronize() != cudaSuccess) return tc_fail("chain kernel failed at %s: %s", o3.name.c_str(), cudaGetErrorString(cudaGetLastError()));
         for (int rep = 0; rep < 3; ++rep) {
@@ -3064,6 +3163,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
           fprintf(stderr, "[tune] chain %s + %s%s%s: fused %.4f ms, separate %.4f ms -> %s\n", o3.name.c_str(), oe.name.c_str(),
                   o3.chain_red >= 0 ? " + " : "", o3.chain_red >= 0 ? net.ops[o3.chain_red].name.c_str() : "", cp.ms, cp.ms_separate,
                   use ? "fused" : "separate");
+        chosen[i].chain = use ? 1 : 0;
       }
       if (!use) continue;
       plan->chains[i] = cp;
@@ -3071,6 +3171,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
       if (o3.chain_red >= 0) plan->chained[o3.chain_red] = 1;
     }
   }
+  if (autotune && !have_cache && !over_budget) tune_store(key, chosen);
   if (autotune) {
     cudaEventDestroy(ev0);
     cudaEventDestroy(ev1);

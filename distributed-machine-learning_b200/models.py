@@ -70,7 +70,8 @@ def get_engine(model_name: str, device: int | None = None) -> Engine:
 def _pool():
     global _decode_pool
     if _decode_pool is None:
-        _decode_pool = ThreadPoolExecutor(max_workers=min(32, os.cpu_count() or 4))  # Pillow releases the GIL while it decodes
+        n = int(os.environ.get("DML_B200_DECODE_THREADS", "0")) or min(32, os.cpu_count() or 4)
+        _decode_pool = ThreadPoolExecutor(max_workers=n)  # Pillow releases the GIL while it decodes
     return _decode_pool
 
 
