@@ -337,6 +337,7 @@ struct TcV2Params {
   int M_cap;        // rows of the output / residual tensors
   int kb1;          // k-blocks of the first GEMM source; [kb1, num_kb) come from the second one (pair kernel)
   int stride2, a2_tiled, in2_row0;
+  int norelu_cols;  // output columns [0, norelu_cols) keep their sign (no ReLU): multiple of 16
 };
 
 __device__ long long g_tc2_prof[160 * 8];
@@ -578,7 +579,7 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) conv_tc2_kernel(const __grid_c
                 f[2 * i + 1] += __uint_as_float(rr[i] & 0xffff0000u);  // high bf16
               }
             }
-            if (p.relu) {
+            if (p.relu && n0 + c0 + gg >= p.norelu_cols) {
 #pragma unroll
               for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
             }
@@ -1520,7 +1521,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
                 f[2 * i + 1] += __uint_as_float(rr[i] & 0xffff0000u);
               }
             }
-            if (p.relu) {
+            if (p.relu && n0 + c0 + gg >= p.norelu_cols) {
 #pragma unroll
               for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
             }
@@ -2532,6 +2533,7 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
 
 int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s) {
   if (!op.valid) return tc_fail("conv plan is not valid");
+  if (p.norelu_cols > 0 && op.version != 2 && op.version != 4) return tc_fail("only the persistent GEMM kernels take ReLU-free output columns");
   if (op.version == 5) {
     TcV5Params k{};
     k.bias = p.bias;
@@ -2687,6 +2689,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.bn = op.bn; k.res_pitch = p.res_pitch; k.relu = p.relu;
     k.stages = op.stages; k.tmem_cols = op.tmem_cols; k.acc_stride = op.acc_stride;
     k.group = op.group;
+    k.norelu_cols = p.norelu_cols;
     k.m_tiles = pair ? (k.M + 2 * BLOCK_M - 1) / (2 * BLOCK_M) : (k.M + BLOCK_M - 1) / BLOCK_M;
     k.n_tiles = p.cout / op.bn;
     k.cw = op.cw;
@@ -3042,6 +3045,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     p.cin_pad = op.cin_pad;
     p.bias = reinterpret_cast<const float*>(wts + op.merged_b_off);
     p.relu = op.relu;
+    p.norelu_cols = op.norelu_cols;
     if (op.in2 >= 0) {
       const Tensor& t2 = net.tensors[op.in2];
       if (t2.buf < 0) return tc_fail("second GEMM source of %s is not an arena tensor", op.name.c_str());
@@ -3079,6 +3083,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     seen.push_back({plan->ops[i].version, plan->ops[i].bn, plan->ops[i].group});
     for (int version : {4, 2, 5, 6, 7}) {
       if (op.in2 >= 0 && version != 4) continue;  // only the pair kernel reads a second GEMM source
+      if (op.norelu_cols > 0 && version != 4 && version != 2) continue;  // ReLU-free leading columns: persistent GEMM kernels only
       for (int bn : {0, 256, 128, 64}) {
         if (version == 5 && (bn != 0 || cout_x > 128 || op.res >= 0)) continue;
         if (version == 6 && bn != 0) continue;

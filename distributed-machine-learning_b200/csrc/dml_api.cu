@@ -171,7 +171,7 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
       p.ho = to.h; p.wo = to.w; p.cout = cout_x; p.out_pitch = to.c_pitch;
       p.res_pitch = op.res >= 0 ? net.tensors[op.res].c_pitch : 0;
       p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;
-      p.cin_pad = op.cin_pad; p.relu = op.relu;
+      p.cin_pad = op.cin_pad; p.relu = op.relu; p.norelu_cols = op.norelu_cols;
       if (op.in2 >= 0) {
         const dml::Tensor& t2 = net.tensors[op.in2];
         p.in2 = e->tensor_ptr(op.in2, img0);
@@ -206,6 +206,10 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
       p.n = cnt; p.hi = ti.h; p.wi = ti.w; p.c = ti.c; p.in_pitch = ti.c_pitch;
       p.ho = to.h; p.wo = to.w; p.out_pitch = to.c_pitch;
       p.k = op.kh; p.stride = op.stride; p.pad = op.pad_h;
+      if (op.pool_bias_of >= 0) {  // the pool branch's 1x1 conv ran first (inside the head GEMM): its folded bias and ReLU come here
+        p.bias = reinterpret_cast<const float*>(e->wts + net.ops[op.pool_bias_of].post_bias_off);
+        p.relu = 1;
+      }
       if (op.kind == dml::OP_MAXPOOL) dml::launch_maxpool(p, e->fp32, s);
       else dml::launch_avgpool(p, e->fp32, s);
       e->launches += 1;
@@ -339,7 +343,7 @@ int dml_create(int device, int model, int max_batch, int micro_batch, int flags,
   std::string err;
   // projection shortcuts folded into the block's last conv: tensor-core engines only (the CUDA-core kernel has one source)
   const bool fuse_sc = e->use_tc && !e->keep_all && getenv("DML_NO_FUSE_SHORTCUT") == nullptr;
-  if (!dml::build_net(model, e->keep_all, e->fp32 ? 4 : 2, !e->fp32, fuse_sc, &e->net, &err)) {
+  if (!dml::build_net(model, e->keep_all, e->fp32 ? 4 : 2, !e->fp32, fuse_sc, &e->net, &err, getenv("DML_NO_POOL_COMMUTE") == nullptr)) {
     delete e;
     return fail(DML_EINVAL, "%s", err.c_str());
   }
@@ -438,6 +442,10 @@ int dml_load_weights(dml_engine* e, const float* blob, size_t num_floats) {
       // BN folded into the conv: s = gamma / sqrt(var + eps); W' = W*s; b' = beta + (b - mean)*s
       double s = (gamma ? (double)gamma[co] : 1.0) / std::sqrt((double)var[co] + (double)op.eps);
       bout[co] = (float)((double)beta[co] + ((bias ? (double)bias[co] : 0.0) - (double)mean[co]) * s);
+      if (op.post_pool) {  // added by the pool op after averaging, not by the GEMM (graph.h, Op::post_pool)
+        reinterpret_cast<float*>(host.data() + op.post_bias_off)[co] = bout[co];
+        bout[co] = 0.f;
+      }
       const size_t row_k = (size_t)taps * op.cin_pad + (size_t)op.cin2_pad;  // packed K of one output channel
       if (op.in2 >= 0) {
         // folded projection shortcut: its own BN scale on its columns [taps * cin_pad, + cin2), its folded bias added

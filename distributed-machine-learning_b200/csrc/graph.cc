@@ -16,6 +16,7 @@ struct Builder {
   bool keep_all;
   int nconv = 0;  // InceptionV3 auto-naming counter
   bool fuse_shortcut = false;
+  bool pool_commute = false;  // InceptionV3 pool branches: 1x1 conv first (inside the merged head GEMM), average pool after
 
   int add_warr(const std::string& name, std::initializer_list<int64_t> shape) {
     WeightArr a;
@@ -136,8 +137,9 @@ struct Builder {
   // Block head with a 1x1 branch that goes straight into the concat: [reduction 1 | reduction 2 | concat] share ONE buffer,
   // the two reductions in R = f1 + f2 scratch channels in FRONT of the concat, so that (red1, red2, branch1x1) are one
   // contiguous channel range = one GEMM.  The block's output tensor is the view behind the scratch channels.
-  struct Head { int cat = -1, b1 = -1, v1 = -1, v2 = -1, merged = -1, lead = -1, R = 0, f1 = 0, f2 = 0, fb1 = 0; };
-  Head head_begin(int x, const std::string& n, int fb1, int f1, int f2, int ccat) {
+  struct Head { int cat = -1, b1 = -1, v1 = -1, v2 = -1, merged = -1, lead = -1, R = 0, f1 = 0, f2 = 0, fb1 = 0, P = 0, vp = -1; };
+  // fp: filters of the pool branch's 1x1 conv (0 = none / not commuted): its pre-pool output takes the first fp scratch channels
+  Head head_begin(int x, const std::string& n, int fb1, int f1, int f2, int ccat, int fp = 0) {
     Head h;
     h.f1 = f1; h.f2 = f2; h.fb1 = fb1;
     const Tensor tx = net->tensors[x];
@@ -146,14 +148,38 @@ struct Builder {
       h.b1 = view(h.cat, n + ":b1", 0, fb1);
       return h;
     }
-    h.R = f1 + f2;
+    h.P = pool_commute ? fp : 0;
+    h.R = h.P + f1 + f2;
     const int buf = new_tensor(n + ":buf", tx.h, tx.w, h.R + ccat);
     h.cat = view(buf, n, h.R, ccat);
     h.b1 = view(buf, n + ":b1", h.R, fb1);
-    h.v1 = view(buf, n + ":red:a", 0, f1);
-    h.v2 = view(buf, n + ":red:b", f1, f2);
+    if (h.P) h.vp = view(buf, n + ":prepool", 0, h.P);
+    h.v1 = view(buf, n + ":red:a", h.P, f1);
+    h.v2 = view(buf, n + ":red:b", h.P + f1, f2);
     h.merged = view(buf, n + ":head", 0, h.R + fb1);
     return h;
+  }
+  // The pool branch of a block: AveragePooling2D(3, 1, same) -> conv2d_bn(f, 1, 1) into the concat slice at c_off.
+  void pool_branch(int x, Head& h, const std::string& n, int c_off, int f) {
+    if (h.P == 0) {
+      int t = pool(OP_AVGPOOL, x, -1, n + ":avgpool", 3, 1, 1);
+      cb(t, cat_view(h, n + ":bp", c_off, f), f, 1, 1);
+      return;
+    }
+    // commuted: the 1x1 conv (no bias, no ReLU) is one more member of the head GEMM, the pool follows on its f channels
+    cb(x, h.vp, f, 1, 1);
+    const int ci = (int)net->ops.size() - 1;
+    net->ops[ci].skip = true;
+    net->ops[ci].merge_row0 = 0;
+    net->ops[ci].post_pool = true;
+    net->ops[h.lead].followers.push_back(ci);
+    net->ops[h.lead].norelu_cols = h.P;
+    const int pi_out = pool(OP_AVGPOOL, h.vp, cat_view(h, n + ":bp", c_off, f), n + ":avgpool", 3, 1, 1);
+    (void)pi_out;
+    Op& po = net->ops.back();
+    po.pool_bias_of = ci;
+    po.relu = true;
+    touch(h.merged, h.lead);  // (the leader writes the scratch channels)
   }
   int cat_view(const Head& h, const std::string& name, int c_off, int c) { return view(h.cat, name, h.R + c_off, c); }
   void head_b1(int x, Head& h) {  // branch1x1: first in Keras' layer order, so it leads the group
@@ -169,7 +195,7 @@ struct Builder {
     if (h.merged >= 0) {
       const int i = (int)net->ops.size() - 1;
       net->ops[i].skip = true;
-      net->ops[i].merge_row0 = which == 0 ? 0 : h.f1;
+      net->ops[i].merge_row0 = h.P + (which == 0 ? 0 : h.f1);
       net->ops[h.lead].followers.push_back(i);
     }
     return out;
@@ -315,15 +341,14 @@ void build_inception_v3(Builder& b) {
   for (int i = 0; i < 3; ++i) {  // mixed0..2, 35x35
     std::string n = "mixed" + std::to_string(i);
     const Tensor tx = net->tensors[x];
-    Builder::Head hd = b.head_begin(x, n, 64, 48, 64, 64 + 64 + 96 + pool_f[i]);
+    Builder::Head hd = b.head_begin(x, n, 64, 48, 64, 64 + 64 + 96 + pool_f[i], pool_f[i]);
     b.head_b1(x, hd);
     int t = b.head_red(x, hd, 0);
     b.cb(t, b.cat_view(hd, n + ":b5", 64, 64), 64, 5, 5);
     t = b.head_red(x, hd, 1);
     t = b.cb(t, -1, 96, 3, 3);
     b.cb(t, b.cat_view(hd, n + ":b3d", 128, 96), 96, 3, 3);
-    t = b.pool(OP_AVGPOOL, x, -1, n + ":avgpool", 3, 1, 1);
-    b.cb(t, b.cat_view(hd, n + ":bp", 224, pool_f[i]), pool_f[i], 1, 1);
+    b.pool_branch(x, hd, n, 224, pool_f[i]);
     x = hd.cat;
   }
   {  // mixed3, 17x17
@@ -342,7 +367,7 @@ void build_inception_v3(Builder& b) {
     std::string n = "mixed" + std::to_string(i + 4);
     const Tensor tx = net->tensors[x];
     int c = c7[i];
-    Builder::Head hd = b.head_begin(x, n, 192, c, c, 768);
+    Builder::Head hd = b.head_begin(x, n, 192, c, c, 768, 192);
     b.head_b1(x, hd);
     int t = b.head_red(x, hd, 0);
     t = b.cb(t, -1, c, 1, 7);
@@ -352,8 +377,7 @@ void build_inception_v3(Builder& b) {
     t = b.cb(t, -1, c, 1, 7);
     t = b.cb(t, -1, c, 7, 1);
     b.cb(t, b.cat_view(hd, n + ":b7d", 384, 192), 192, 1, 7);
-    t = b.pool(OP_AVGPOOL, x, -1, n + ":avgpool", 3, 1, 1);
-    b.cb(t, b.cat_view(hd, n + ":bp", 576, 192), 192, 1, 1);
+    b.pool_branch(x, hd, n, 576, 192);
     x = hd.cat;
   }
   {  // mixed8, 8x8
@@ -373,7 +397,7 @@ void build_inception_v3(Builder& b) {
   for (int i = 9; i <= 10; ++i) {  // mixed9, mixed10, 8x8
     std::string n = "mixed" + std::to_string(i);
     const Tensor tx = net->tensors[x];
-    Builder::Head hd = b.head_begin(x, n, 320, 384, 448, 2048);
+    Builder::Head hd = b.head_begin(x, n, 320, 384, 448, 2048, 192);
     b.head_b1(x, hd);
     int t = b.head_red(x, hd, 0);
     b.cb(t, b.cat_view(hd, n + ":b3a", 320, 384), 384, 1, 3);
@@ -382,8 +406,7 @@ void build_inception_v3(Builder& b) {
     t = b.cb(t, -1, 384, 3, 3);
     b.cb(t, b.cat_view(hd, n + ":bda", 1088, 384), 384, 1, 3);
     b.cb(t, b.cat_view(hd, n + ":bdb", 1472, 384), 384, 3, 1);
-    t = b.pool(OP_AVGPOOL, x, -1, n + ":avgpool", 3, 1, 1);
-    b.cb(t, b.cat_view(hd, n + ":bp", 1856, 192), 192, 1, 1);
+    b.pool_branch(x, hd, n, 1856, 192);
     x = hd.cat;
   }
   b.head(x);
@@ -450,6 +473,11 @@ void plan_weights(Net* net, int wbytes, bool tc_pad) {
       f.bias_off = op.merged_b_off + (int64_t)f.merge_row0 * 4;
     }
   }
+  for (Op& op : net->ops)
+    if (op.kind == OP_CONV && op.post_pool) {  // the bias the pool op adds after averaging
+      op.post_bias_off = off;
+      off = align_up(off + (int64_t)op.cout * 4, 256);
+    }
   // floor division by 2 of (tap - pad): cells a in [a_min, a_max] of the space-to-depth grid
   auto fdiv2 = [](int v) { return v >= 0 ? v / 2 : -((-v + 1) / 2); };
   if (tc_pad && !net->ops.empty()) {
@@ -472,11 +500,12 @@ void plan_weights(Net* net, int wbytes, bool tc_pad) {
   net->weights_bytes = off;
 }
 
-bool build(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut, bool spec_only, Net* net, std::string* err) {
+bool build(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut, bool spec_only, Net* net, std::string* err, bool pool_commute) {
   *net = Net();
   net->model = model;
   Builder b{net, keep_all};
   b.fuse_shortcut = fuse_shortcut && !keep_all && tc_pad;
+  b.pool_commute = b.fuse_shortcut && pool_commute;
   Tensor in;
   in.name = "input";
   in.buf = -1;
@@ -501,11 +530,11 @@ bool build(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut
 
 }  // namespace
 
-bool build_net(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut, Net* net, std::string* err) {
-  return build(model, keep_all, wbytes, tc_pad, fuse_shortcut, false, net, err);
+bool build_net(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut, Net* net, std::string* err, bool pool_commute) {
+  return build(model, keep_all, wbytes, tc_pad, fuse_shortcut, false, net, err, pool_commute);
 }
 bool build_weight_spec(int model, Net* net, std::string* err) {
-  return build(model, true, 4, false, false, true, net, err);
+  return build(model, true, 4, false, false, true, net, err, false);
 }
 
 }  // namespace dml

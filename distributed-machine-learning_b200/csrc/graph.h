@@ -62,6 +62,15 @@ struct Op {
   // 1x1 expand (chain_exp) and the next block's 1x1 reduce (chain_red, -1 for the stage's last block); chain_lead on
   // the members points back.  The engine decides at plan time whether the fused kernel or the separate ones run.
   int chain_exp = -1, chain_red = -1, chain_lead = -1;
+  // InceptionV3's pool branch is AveragePooling2D -> 1x1 conv -> BN -> ReLU.  The pool and the 1x1 conv are both linear and act
+  // on different axes (space / channels), so they commute: relu(conv(avgpool(x)) + b) == relu(avgpool(conv(x)) + b).  In fused
+  // engines the conv (post_pool = true) joins the block's merged head GEMM WITHOUT bias and ReLU (its output channels come first
+  // in the merged range: Op::norelu_cols of the leader) and the pool runs afterwards on the conv's few output channels instead of
+  // on the block's wide input, adding the folded bias (post_bias_off) and the ReLU.  pool_bias_of: on the pool op, the conv.
+  bool post_pool = false;
+  int64_t post_bias_off = 0;
+  int norelu_cols = 0;
+  int pool_bias_of = -1;
   int in2 = -1, cin2 = 0, cin2_pad = 0, stride2 = 1;
   int w2_kernel = -1, w2_bias = -1, w2_gamma = -1, w2_beta = -1, w2_mean = -1, w2_var = -1;
   float eps2 = 0.f;
@@ -99,7 +108,7 @@ struct Net {
 // tc_pad: pad Cin of tensor-core-eligible convs to a multiple of 64.
 // fuse_shortcut: ResNet50's projection shortcuts become a second GEMM source of the block's last conv (Op::in2) and
 // InceptionV3's sibling 1x1 branch heads become one GEMM (Op::followers).
-bool build_net(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut, Net* net, std::string* err);
+bool build_net(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut, Net* net, std::string* err, bool pool_commute = true);
 
 // Only the weight-array list (cheap; for dml_model_* queries).
 bool build_weight_spec(int model, Net* net, std::string* err);

@@ -275,7 +275,14 @@ __global__ void __launch_bounds__(256) pool_kernel(PoolParams p) {
   }
   T o[V];
 #pragma unroll
-  for (int i = 0; i < V; ++i) o[i] = from_f<T>(AVG ? acc[i] / (float)valid : acc[i]);
+  for (int i = 0; i < V; ++i) {
+    float v = AVG ? acc[i] / (float)valid : acc[i];
+    if (AVG && p.bias) {  // pool branch with the 1x1 conv in front (PoolParams::bias)
+      v += __ldg(p.bias + g * V + i);
+      if (p.relu) v = fmaxf(v, 0.f);
+    }
+    o[i] = from_f<T>(v);
+  }
   T* out = reinterpret_cast<T*>(p.out) + (((int64_t)n * p.ho + ho) * p.wo + wo) * p.out_pitch + g * V;
   *reinterpret_cast<uint4*>(out) = *reinterpret_cast<uint4*>(o);
 }
@@ -351,8 +358,12 @@ __global__ void __launch_bounds__(256) avgpool3_kernel(PoolParams p) {
   const float ncols = (float)(w1 - w0 + 1);
   const int r_begin = seg * AVG_ROWS, r_end = r_begin + AVG_ROWS < p.hi ? r_begin + AVG_ROWS : p.hi;
   float h0[V], h1[V], h2[V];  // horizontal sums of rows r-1, r, r+1
+  float bv[V];
 #pragma unroll
-  for (int i = 0; i < V; ++i) h0[i] = h1[i] = h2[i] = 0.f;
+  for (int i = 0; i < V; ++i) {
+    h0[i] = h1[i] = h2[i] = 0.f;
+    bv[i] = p.bias ? __ldg(p.bias + g * V + i) : 0.f;
+  }
   auto hsum = [&](int r, float (&h)[V]) {
     uint4 raw[3];
 #pragma unroll
@@ -387,7 +398,12 @@ __global__ void __launch_bounds__(256) avgpool3_kernel(PoolParams p) {
     for (int i = 0; i < V; ++i) {
       // h0 is all zeros above the first row and h2 below the last one: adding them is exact
       float sum = h1[i] + h0[i] + h2[i];
-      o[i] = from_f<T>(sum * inv);
+      float v = sum * inv;
+      if (p.bias) {  // pool branch with the 1x1 conv in front: folded bias and ReLU come after the average
+        v += bv[i];
+        if (p.relu) v = fmaxf(v, 0.f);
+      }
+      o[i] = from_f<T>(v);
     }
     *reinterpret_cast<uint4*>(out + (r * p.wi + wo) * p.out_pitch) = *reinterpret_cast<uint4*>(o);
 #pragma unroll

@@ -142,6 +142,7 @@ def test_merged_sibling_reductions_are_bit_identical(images, monkeypatch):
     W = kw.generate("InceptionV3", "folding_stress", 11)
     sel = images[50:69]
     outs = []
+    monkeypatch.setenv("DML_NO_POOL_COMMUTE", "1")  # the pool-branch commute (next test) changes the rounding order, this merge does not
     for fuse in (True, False):
         if fuse:
             monkeypatch.delenv("DML_NO_FUSE_SHORTCUT", raising=False)
@@ -156,6 +157,39 @@ def test_merged_sibling_reductions_are_bit_identical(images, monkeypatch):
         finally:
             eng.close()
     assert np.array_equal(outs[0], outs[1])
+
+
+def test_pool_branch_conv_before_pool_matches_pool_before_conv(images, monkeypatch):
+    """InceptionV3's pool branches are AveragePooling2D -> 1x1 conv -> BN -> ReLU (Keras conv2d_bn after the pool).  The engine
+    runs the 1x1 conv first, as one more member of the block's merged head GEMM, and averages its few output channels
+    afterwards (bias and ReLU after the average): the same linear map, with the bf16 rounding at a different place.  Against
+    the pool-first order on weights with non-trivial BN statistics, and against the fp32 oracle."""
+    from oracle import models_ref
+    kw = pkg("keras_weights")
+    W = kw.generate("InceptionV3", "he_uniform", 7)
+    sel = images[100:124]
+    outs = {}
+    for commute in (True, False):
+        if commute:
+            monkeypatch.delenv("DML_NO_POOL_COMMUTE", raising=False)
+        else:
+            monkeypatch.setenv("DML_NO_POOL_COMMUTE", "1")
+        eng = pkg("engine").Engine("InceptionV3", max_batch=24, weights=W)
+        try:
+            followers = [o[0] for o in eng.ops() if o[1] == 0 and o[3] == 0]
+            assert len(followers) == (28 if commute else 19), followers  # + the 9 pool-branch convs
+            _, _, probs = eng.predict_images(sel, want_probs=True)
+            outs[commute] = (probs, eng.logits(len(sel)).cpu().numpy().copy())
+        finally:
+            eng.close()
+    ref_probs, ref_logits = models_ref.predict_arrays("InceptionV3", sel, W, batch=8)
+    scale = np.abs(ref_logits).max()
+    d_orders = np.abs(outs[True][1] - outs[False][1]).max() / scale
+    d_ref = {c: np.abs(outs[c][1] - ref_logits).max() / scale for c in (True, False)}
+    print(f"\npool-branch order: conv-first vs pool-first logits rel {d_orders:.2e}; vs oracle: conv-first {d_ref[True]:.2e}, pool-first {d_ref[False]:.2e}")
+    assert d_orders <= 2e-2
+    assert d_ref[True] <= 3e-2 and np.abs(outs[True][0] - ref_probs).max() <= 2e-2
+    assert (outs[True][0].argmax(1) == ref_probs.argmax(1)).all()
 
 
 def test_folding_stress_fp32(images):
