@@ -338,6 +338,7 @@ struct TcV2Params {
   int kb1;          // k-blocks of the first GEMM source; [kb1, num_kb) come from the second one (pair kernel)
   int stride2, a2_tiled, in2_row0;
   int norelu_cols;  // output columns [0, norelu_cols) keep their sign (no ReLU): multiple of 16
+  int rev;          // walk the tiles from the last to the first (see ConvParams::rev)
 };
 
 __device__ long long g_tc2_prof[160 * 8];
@@ -417,7 +418,8 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) conv_tc2_kernel(const __grid_c
     const long long prof_t0 = p.prof ? clock64() : 0;
     const uint32_t chunk_bytes = (uint32_t)BLOCK_M * (uint32_t)p.cw * 2u;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-      const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
+      const int tix = p.rev ? total_tiles - 1 - tile : tile;
+      const int mt = tix / p.n_tiles, nt = tix - mt * p.n_tiles;
       const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
       if (p.has_res) {
         // whole residual tile of this output tile, one box per column chunk
@@ -527,7 +529,8 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) conv_tc2_kernel(const __grid_c
     const uint32_t swz = cw == 64 ? (uint32_t)(lane & 7) : (cw == 32 ? (uint32_t)((lane >> 1) & 3) : (uint32_t)((lane >> 2) & 1));
     uint32_t lt = 0, nstore = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-      const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
+      const int tix = p.rev ? total_tiles - 1 - tile : tile;
+      const int mt = tix / p.n_tiles, nt = tix - mt * p.n_tiles;
       const int m0 = mt * BLOCK_M, n0 = nt * p.bn;
       const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
       if (p.has_res) mbar_wait(rfull0 + 8u * a, aph);
@@ -875,14 +878,22 @@ constexpr int TC6_THREADS = 320;  // producer warp, MMA warp, 8 epilogue warps
 
 // (image, tile inside the image) of a persistent CTA's tiles without a division per tile
 struct TileWalk {
-  int img, mt, tpi, dimg, dmt;
-  __device__ TileWalk(int tiles_per_img, int first, int stride) : tpi(tiles_per_img) {
+  int img, mt, tpi, dimg, dmt, rev;
+  // rev: walk from tile total - 1 - first downwards (ConvParams::rev)
+  __device__ TileWalk(int tiles_per_img, int first, int stride, int total = 0, int reverse = 0) : tpi(tiles_per_img), rev(reverse) {
+    if (rev) first = total - 1 - first;
+    if (first < 0) first = 0;  // (a CTA without tiles never uses the walk)
     img = first / tpi; mt = first - img * tpi;
     dimg = stride / tpi; dmt = stride - dimg * tpi;
   }
   __device__ void next() {
-    img += dimg; mt += dmt;
-    if (mt >= tpi) { mt -= tpi; ++img; }
+    if (!rev) {
+      img += dimg; mt += dmt;
+      if (mt >= tpi) { mt -= tpi; ++img; }
+    } else {
+      img -= dimg; mt -= dmt;
+      if (mt < 0) { mt += tpi; --img; }
+    }
   }
 };
 
@@ -903,6 +914,7 @@ struct TcV6Params {
   int n_acc;       // TMEM accumulators (2 or 4)
   int n_tiles;     // Cout / bn
   float inv_wp;    // 1 / wp
+  int rev;         // walk the tiles from the last to the first (ConvParams::rev)
 };
 
 // q / wp for 0 <= q < 2^16 and wp <= 256 without an integer division: (q + 0.5) / wp is at least 0.5 / 256 away from
@@ -982,7 +994,7 @@ __global__ void __launch_bounds__(TC6_THREADS, 1) conv_tc6_kernel(const __grid_c
     __syncwarp();
     uint32_t ita = 0;
     const uint32_t box_bytes = (uint32_t)p.rows_box * (uint32_t)p.wp * row_bytes;
-    TileWalk tw(p.tiles_per_img, vcta, vgrid);
+    TileWalk tw(p.tiles_per_img, vcta, vgrid, total_tiles, p.rev);
     uint32_t sa = 0, pha = 0;
     for (int tile = vcta; tile < total_tiles; tile += vgrid, ++ita, tw.next(), pha ^= (++sa == (uint32_t)p.a_stages), sa = sa == (uint32_t)p.a_stages ? 0u : sa) {
       const int img = tw.img;
@@ -1009,7 +1021,7 @@ __global__ void __launch_bounds__(TC6_THREADS, 1) conv_tc6_kernel(const __grid_c
     const int ksteps = p.row_bytes >> 5;
     mbar_wait(bfull, 0);
     uint32_t ita = 0;
-    TileWalk tw(p.tiles_per_img, vcta, vgrid);
+    TileWalk tw(p.tiles_per_img, vcta, vgrid, total_tiles, p.rev);
     uint32_t sa = 0, pha = 0;
     for (int tile = vcta; tile < total_tiles; tile += vgrid, ++ita, tw.next(), pha ^= (++sa == (uint32_t)p.a_stages), sa = sa == (uint32_t)p.a_stages ? 0u : sa) {
       const int l0 = tw.mt * BLOCK_M;
@@ -1094,7 +1106,7 @@ __global__ void __launch_bounds__(TC6_THREADS, 1) conv_tc6_kernel(const __grid_c
     named_bar_sync(1, 256);
     const int g_begin = 0, g_end = p.bn;
     uint32_t lt = (uint32_t)grp;
-    TileWalk tw(p.tiles_per_img, vcta + grp * vgrid, 2 * vgrid);
+    TileWalk tw(p.tiles_per_img, vcta + grp * vgrid, 2 * vgrid, total_tiles, p.rev);
     for (int tile = vcta + grp * vgrid; tile < total_tiles; tile += 2 * vgrid, lt += 2, tw.next()) {
       const int img = tw.img;
       const int l0 = tw.mt * BLOCK_M;
@@ -1328,7 +1340,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
     const long long prof_p0 = p.prof ? clock64() : 0;
     const uint32_t chunk_bytes = (uint32_t)BLOCK_M * (uint32_t)p.cw * 2u;
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
-      const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
+      const int tix = p.rev ? total_tiles - 1 - tile : tile;
+      const int mt = tix / p.n_tiles, nt = tix - mt * p.n_tiles;
       const int m0 = mt * 2 * BLOCK_M + (int)rank * BLOCK_M, n0 = nt * p.bn;
       if (p.has_res == 1) {
         const uint32_t rb = lt & 1u, rph = (lt >> 1) & 1u;
@@ -1470,7 +1483,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
     const uint32_t swz = cw == 64 ? (uint32_t)(lane & 7) : (cw == 32 ? (uint32_t)((lane >> 1) & 3) : (uint32_t)((lane >> 2) & 1));
     uint32_t lt = 0, nstore = 0;
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
-      const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
+      const int tix = p.rev ? total_tiles - 1 - tile : tile;
+      const int mt = tix / p.n_tiles, nt = tix - mt * p.n_tiles;
       const int m0 = mt * 2 * BLOCK_M + (int)rank * BLOCK_M, n0 = nt * p.bn;
       const uint32_t a = lt & 1u, aph = (lt >> 1) & 1u;
       if (p.has_res == 1) mbar_wait(rfull0 + 8u * a, aph);
@@ -1583,6 +1597,7 @@ struct TcV6xParams {
   int in_img0, out_img0;
   int row_bytes, last_kmma, cin_pad, wide_store;
   float inv_wp;
+  int rev;  // walk the tiles from the last to the first (ConvParams::rev)
 };
 
 __device__ __forceinline__ void tma2_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
@@ -1654,7 +1669,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC6_THREADS, 1)
     __syncwarp();
     uint32_t ita = 0, sa = 0, pha = 0;
     const uint32_t box_bytes = (uint32_t)p.rows_box * (uint32_t)p.wp * row_bytes;
-    TileWalk tw(p.ptiles_per_img, vcl, vn);
+    TileWalk tw(p.ptiles_per_img, vcl, vn, total_tiles, p.rev);
     for (int tile = vcl; tile < total_tiles; tile += vn, ++ita, tw.next(), pha ^= (++sa == (uint32_t)p.a_stages), sa = sa == (uint32_t)p.a_stages ? 0u : sa) {
       const int row0 = (tw.mt * 2 + (int)rank) * p.rpt;  // first output row of this CTA's tile (may be past the image: zero fill)
       mbar_wait(aempty0 + 8u * sa, pha ^ 1u);
@@ -1741,7 +1756,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC6_THREADS, 1)
     named_bar_sync(1, 256);
     const int trow = div_wp(et, p.inv_wp), tcol = et - trow * p.wp;  // the same for every tile
     uint32_t lt = (uint32_t)grp;
-    TileWalk tw(p.ptiles_per_img, vcl + grp * vn, 2 * vn);
+    TileWalk tw(p.ptiles_per_img, vcl + grp * vn, 2 * vn, total_tiles, p.rev);
     for (int tile = vcl + grp * vn; tile < total_tiles; tile += 2 * vn, lt += 2, tw.next()) {
       const uint32_t a = lt & (n_acc - 1u), aph = (lt >> acc_shift) & 1u;
       const int orow = (tw.mt * 2 + (int)rank) * p.rpt + trow;
@@ -2577,6 +2592,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.cin_pad = p.cin_pad;
     k.inv_wp = 1.0f / (float)op.wp;
     k.wide_store = (p.out_pitch % 16 == 0 && reinterpret_cast<uintptr_t>(p.out) % 32 == 0) ? 1 : 0;
+    k.rev = p.rev;
     const int tiles = p.n * op.tiles_per_img;
     const int pairs = g_num_sms / 2 / k.n_tiles;
     const int vn = tiles < pairs ? tiles : pairs;
@@ -2616,6 +2632,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     const int grid = vgrid * k.n_tiles;
     k.n_acc = op.tmem_cols / op.acc_stride;
     k.inv_wp = 1.0f / (float)op.wp;
+    k.rev = p.rev;
     k.wide_store = (p.out_pitch % 16 == 0 && reinterpret_cast<uintptr_t>(p.out) % 32 == 0 && !getenv("DML_NO_WIDE_STORE")) ? 1 : 0;
     if (getenv("DML_V6_NOSTORE")) k.wide_store = 2;  // experiment: skip the epilogue's global stores
     static const bool prof6 = getenv("DML_TC_PROF") != nullptr;
@@ -2690,6 +2707,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.stages = op.stages; k.tmem_cols = op.tmem_cols; k.acc_stride = op.acc_stride;
     k.group = op.group;
     k.norelu_cols = p.norelu_cols;
+    k.rev = p.rev;
     k.m_tiles = pair ? (k.M + 2 * BLOCK_M - 1) / (2 * BLOCK_M) : (k.M + BLOCK_M - 1) / BLOCK_M;
     k.n_tiles = p.cout / op.bn;
     k.cw = op.cw;
@@ -2833,6 +2851,7 @@ int launch_chain(const ChainPlan& pl, const ChainArgs& a, cudaStream_t s) {
   k.inv_wp = 1.0f / (float)pl.wp;
   static const int ahead_env = getenv("DML_CHAIN_AHEAD") ? atoi(getenv("DML_CHAIN_AHEAD")) : 2;
   k.ahead = ahead_env == 1 ? 1 : 2;
+  k.rev = a.rev;
   static const bool prof = getenv("DML_CHAIN_PROF") != nullptr;
   k.prof = prof ? 1 : 0;
   if (prof) {
@@ -3185,7 +3204,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
   return 0;
 }
 
-int launch_chain_tc(const TcPlan& plan, const Net& net, uint8_t* wts, int lead, int n, uint8_t* ws, size_t off_arena, cudaStream_t s) {
+int launch_chain_tc(const TcPlan& plan, const Net& net, uint8_t* wts, int lead, int n, uint8_t* ws, size_t off_arena, cudaStream_t s, int rev) {
   if (lead < 0 || lead >= (int)plan.chains.size() || !plan.chains[lead].valid) return tc_fail("no chain plan for op %d", lead);
   auto tptr = [&](int t) -> uint8_t* {
     const Tensor& tt = net.tensors[t];
@@ -3193,6 +3212,7 @@ int launch_chain_tc(const TcPlan& plan, const Net& net, uint8_t* wts, int lead, 
   };
   ChainArgs a;
   chain_args(net, wts, lead, n, tptr, &a);
+  a.rev = rev;
   return launch_chain(plan.chains[lead], a, s);
 }
 

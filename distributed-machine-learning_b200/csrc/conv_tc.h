@@ -52,6 +52,7 @@ struct ChainArgs {
   const void* wr = nullptr; const float* br = nullptr;   // next block's reduce: packed [64][256], folded bias; or nullptr
   void* y1n = nullptr; int y1n_pitch = 0;          // its output [n*h*w][64]
   int n = 0, h = 0, w = 0;
+  int rev = 0;  // ConvParams::rev
 };
 struct ChainPlan {
   bool valid = false;
@@ -92,7 +93,7 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
 int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s);
 int launch_conv_tc(const TcPlan& plan, int op_index, const ConvParams& p, int img0, cudaStream_t s, int* nlaunch);
 // Runs the fused chain led by op `lead` (plan.chains[lead].valid) over the first n images of the arena.
-int launch_chain_tc(const TcPlan& plan, const Net& net, uint8_t* wts, int lead, int n, uint8_t* ws, size_t off_arena, cudaStream_t s);
+int launch_chain_tc(const TcPlan& plan, const Net& net, uint8_t* wts, int lead, int n, uint8_t* ws, size_t off_arena, cudaStream_t s, int rev = 0);
 const char* tc_last_error();
 // Tiled bf16 tensor map (rank <= 5) for kernels outside conv_tc.cu; swizzle_bytes in {0, 32, 64, 128}.
 int tc_make_tiled_map(CUtensorMap* out, void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,

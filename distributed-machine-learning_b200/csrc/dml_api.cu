@@ -151,6 +151,9 @@ int plan_stem(dml_engine* e) {
 
 int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
   const dml::Net& net = e->net;
+  // consecutive launches walk their tiles in opposite directions (kernels.h, ConvParams::rev): K1 ascending, the stem descending, ...
+  static const bool pingpong = getenv("DML_NO_PINGPONG") == nullptr;
+  int rev = 0;
   for (size_t oi = 0; oi < net.ops.size(); ++oi) {
     const dml::Op& op = net.ops[oi];
     if (op.skip) continue;  // computed by its leader (Op::merge_with)
@@ -160,8 +163,10 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
     const dml::Tensor& ti = net.tensors[op.in];
     const dml::Tensor& to = net.tensors[out_t];
     e->prof_begin((int)oi, s);
+    if (pingpong) rev ^= 1;
     if (op.kind == dml::OP_CONV) {
       dml::ConvParams p{};
+      p.rev = rev;
       p.in = e->tensor_ptr(op.in, img0);
       p.w = e->wts + op.merged_w_off;  // = wpack_off unless the op leads a merged group (its rows need not come first)
       p.bias = reinterpret_cast<const float*>(e->wts + op.merged_b_off);
@@ -180,11 +185,12 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
       int nl = 0;
       if (e->use_tc && oi < e->tc.chains.size() && e->tc.chains[oi].valid) {
         // 3x3 + expand (+ residual / folded shortcut) + the next block's reduce as one kernel
-        if (dml::launch_chain_tc(e->tc, net, e->wts, (int)oi, cnt, e->ws, e->off_arena, s) != 0)
+        if (dml::launch_chain_tc(e->tc, net, e->wts, (int)oi, cnt, e->ws, e->off_arena, s, rev) != 0)
           return fail(DML_ECUDA, "chain kernel launch failed at %s: %s", op.name.c_str(), dml::tc_last_error());
         nl = 1;
       } else if (e->s2d && (int)oi == net.s2d.op) {
         dml::ConvParams p2 = stem_s2d_params(e, img0, cnt);
+        p2.rev = rev;
         if (dml::launch_conv_tc_plan(e->stem_plan, p2, s) != 0)
           return fail(DML_ECUDA, "stem conv launch failed for %s: %s", op.name.c_str(), dml::tc_last_error());
         nl = 1;
@@ -201,6 +207,7 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
       e->launches += nl;
     } else if (op.kind == dml::OP_MAXPOOL || op.kind == dml::OP_AVGPOOL) {
       dml::PoolParams p{};
+      p.rev = rev;
       p.in = e->tensor_ptr(op.in, img0);
       p.out = e->tensor_ptr(op.out, img0);
       p.n = cnt; p.hi = ti.h; p.wi = ti.w; p.c = ti.c; p.in_pitch = ti.c_pitch;

@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(256) maxpool3_bf16_kernel(PoolParams p) {
   // 32-bit index arithmetic (the launcher checks the thread count fits): 64-bit divisions were most of this kernel's
   // instructions (ncu: 67 % issue activity at 62 % of DRAM throughput)
   const uint32_t cg = (uint32_t)p.c >> 3;
-  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t idx = (p.rev ? gridDim.x - 1u - blockIdx.x : blockIdx.x) * blockDim.x + threadIdx.x;  // PoolParams::rev: last pixels first
   if (idx >= (uint32_t)p.n * (uint32_t)p.ho * (uint32_t)p.wo * cg) return;
   const uint32_t pix = idx / cg;
   const int g = (int)(idx - pix * cg);
@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(256) avgpool3_kernel(PoolParams p) {
   const int cg = p.c / V;
   const int segs = (p.hi + AVG_ROWS - 1) / AVG_ROWS;
   // 32-bit index arithmetic (the launcher checks the thread count fits)
-  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t idx = (p.rev ? gridDim.x - 1u - blockIdx.x : blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= (uint32_t)p.n * (uint32_t)segs * (uint32_t)p.wi * (uint32_t)cg) return;
   const uint32_t q1 = idx / (uint32_t)cg;
   const int g = (int)(idx - q1 * (uint32_t)cg);

@@ -18,6 +18,9 @@ struct ConvParams {
   // second GEMM source (graph.h, Op::in2): a 1x1 convolution of stride stride2 over in2, accumulated into the same output
   const void* in2 = nullptr;
   int hi2 = 0, wi2 = 0, cin2 = 0, in2_pitch = 0, stride2 = 1, cin2_pad = 0;
+  // Tile order.  Consecutive layers walk their tiles in OPPOSITE directions: what a layer wrote last is still in L2 (126 MB) when
+  // the next layer starts, so the next layer begins with exactly those pixels instead of with the ones evicted long ago.
+  int rev = 0;
   int norelu_cols = 0;  // output channels [0, norelu_cols) get no ReLU (graph.h, Op::norelu_cols); a multiple of 16
   int in_img0 = 0;   // tcgen05 path: first image / first output row of this launch inside the
   int out_row0 = 0;  // planned tensor maps (the pointers above are already offset for the CUDA-core path)
@@ -29,6 +32,7 @@ struct PoolParams {
   int n, hi, wi, c, in_pitch;
   int ho, wo, out_pitch;
   int k, stride, pad;
+  int rev = 0;                  // walk the outputs from the last to the first (ConvParams::rev)
   const float* bias = nullptr;  // average pool only: per-channel bias added after the average, then ReLU if relu != 0
   int relu = 0;                 // (the pool branch of an Inception block with the 1x1 conv moved in front, graph.h Op::post_pool)
 };
