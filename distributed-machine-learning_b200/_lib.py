@@ -80,6 +80,7 @@ _SIGS = {
                         C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)],
     "dml_input_tensor": [_vp, C.POINTER(_vp), C.POINTER(_i)],
     "dml_input_layout": [_vp, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)],
+    "dml_input_rows": [_vp, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)],
     "dml_logits": [_vp, C.POINTER(_vp)],
     "dml_launch_count": [_vp, C.POINTER(_i64)],
     "dml_num_ops": [_vp, C.POINTER(_i)],

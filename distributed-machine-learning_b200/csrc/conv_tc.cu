@@ -2245,7 +2245,10 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
   }
   // ---- v6: halo kernel with the whole filter resident (few-channel stride-1 multi-tap layers) ----
   if (tune.version == 6 || tune.version == 0) {
-    const int wp = p.wo + p.kw - 1;
+    // in_row_cells: the input rows are physically padded to that many pixels and pre-swizzled (16-channel space-to-depth stems)
+    if (p.in_row_cells && (p.cin != 16 || p.in_pitch != 16 || p.in_row_cells % 8 || p.in_row_cells < p.wo + p.kw - 1 || p.in_row_cells > 256 * 8))
+      return tc_fail("row-padded input needs 16 channels and a row of a multiple of 8 pixels that covers the padded width");
+    const int wp = p.in_row_cells ? p.in_row_cells : p.wo + p.kw - 1;
     const int row_bytes = p.cin <= 16 ? 32 : (p.cin <= 32 ? 64 : 128);
     const int kb = row_bytes / 2;
     const int cblocks = (p.cin + kb - 1) / kb;
@@ -2297,7 +2300,18 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
         cuuint64_t gstr[3] = {(cuuint64_t)p.in_pitch * 2, (cuuint64_t)p.wi * p.in_pitch * 2, (cuuint64_t)p.hi * p.wi * p.in_pitch * 2};
         cuuint32_t box[4] = {(cuuint32_t)kb, (cuuint32_t)wp, (cuuint32_t)v6.rows_box, 1};
         cuuint32_t es[4] = {1, 1, 1, 1};
-        CUresult r6 = g_encode_tiled(&v6.map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p.in), gdim, gstr, box, es,
+        CUresult r6;
+        if (p.in_row_cells) {
+          // rows of wp pixels in memory: view (8 pixels x 16 channels = 256 bytes, wp / 8 groups, rows, images); one box brings the
+          // whole halo in 256-byte lines, copied as is (the pixels are stored swizzled already)
+          cuuint64_t pdim[4] = {128, (cuuint64_t)(wp / 8), (cuuint64_t)p.hi, (cuuint64_t)n_capacity};
+          cuuint64_t pstr[3] = {256, (cuuint64_t)wp * 32, (cuuint64_t)p.hi * wp * 32};
+          cuuint32_t pbox[4] = {128, (cuuint32_t)(wp / 8), (cuuint32_t)v6.rows_box, 1};
+          r6 = g_encode_tiled(&v6.map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p.in), pdim, pstr, pbox, es,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        } else
+        r6 = g_encode_tiled(&v6.map_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p.in), gdim, gstr, box, es,
                                      CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r6 != CUDA_SUCCESS) return tc_fail("cuTensorMapEncodeTiled(halo A, v6) failed (%d): wp=%d rows=%d", (int)r6, wp, v6.rows_box);
@@ -2616,7 +2630,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.out = reinterpret_cast<__nv_bfloat16*>(p.out);
     if (p.n > op.m_capacity) return tc_fail("batch of %d images exceeds the planned capacity", p.n);
     k.n_img = p.n; k.ho = p.ho; k.wo = p.wo; k.wp = op.wp; k.out_pitch = p.out_pitch;
-    k.kh = p.kh; k.kw = p.kw; k.pad_h = p.pad_h; k.pad_w = p.pad_w; k.cblocks = op.cpb;
+    k.kh = p.kh; k.kw = p.kw; k.pad_h = p.pad_h; k.pad_w = p.in_row_cells ? 0 : p.pad_w; k.cblocks = op.cpb;  // (the left padding is in memory)
     k.tiles_per_img = op.tiles_per_img; k.rows_box = op.rows_box;
     k.a_cb_bytes = op.a_cb_bytes; k.a_stage_bytes = op.a_stage_bytes; k.a_stages = op.a_stages;
     k.bn = op.bn; k.relu = p.relu; k.tmem_cols = op.tmem_cols; k.acc_stride = op.acc_stride; k.cw = op.cw;
@@ -2896,8 +2910,8 @@ int launch_chain(const ChainPlan& pl, const ChainArgs& a, cudaStream_t s) {
     struct { const char* name; int first, count; } fam[] = {
         {"producer:halo_empty", 3, 2}, {"producer|B:outc_empty", 19, 4}, {"producer|B:slot_free", 27, 4}, {"producer:s2_empty", 13, 2},
         {"mma:halo_full", 1, 2}, {"mma:acc1_empty", 7, 2}, {"mma:acc2_empty", 33, 1}, {"mma:y2_full", 9, 1}, {"mma:s2_full", 11, 2},
-        {"mma:acc3_empty", 32, 1}, {"mma:outc_full", 15, 4}, {"A:acc1_full", 5, 2}, {"A:y2_free", 34, 1}, {"A:acc3_full", 31, 1},
-        {"B:acc2_full", 10, 1}, {"B:res_full", 23, 4}};
+        {"mma:acc3_empty", 32, 1}, {"mma:outc_full", 15, 1}, {"A:acc1_full", 5, 2}, {"A:y2_free", 34, 1}, {"A:acc3_full", 31, 1},
+        {"B:acc2_full", 10, 1}, {"B:res_full", 23, 4}, {"B:compute", 35, 1}, {"B:fence", 36, 1}, {"B:arrives", 16, 1}, {"B:store_issue", 17, 1}, {"B:store_read", 37, 1}};
     for (const auto& f : fam) {
       double v = 0;
       for (int i = 0; i < f.count; ++i) v += a[f.first + i];

@@ -133,6 +133,7 @@ dml::ConvParams stem_s2d_params(const dml_engine* e, int img0, int cnt) {
   p.out = e->tensor_ptr(op.out, 0);
   p.out_row0 = 0;
   p.n = cnt; p.hi = net.s2d.size; p.wi = net.s2d.size; p.cin = 16; p.in_pitch = 16; p.cin_pad = 16;
+  p.in_row_cells = net.s2d.row_cells;
   p.ho = to.h; p.wo = to.w; p.cout = op.cout; p.out_pitch = to.c_pitch;
   p.kh = net.s2d.k2; p.kw = net.s2d.k2; p.stride = 1; p.pad_h = net.s2d.pad2; p.pad_w = net.s2d.pad2;
   p.relu = op.relu;
@@ -261,6 +262,8 @@ int run_pre(dml_engine* e, const uint8_t* d_pixels, const int64_t* d_img_off, co
   p.n = img0 + cnt; p.S = S; p.caffe = e->net.mode == 0;
   p.img_begin = img0; p.img_end = img0 + cnt;
   p.s2d = e->s2d ? 1 : 0;
+  p.s2d_row_cells = e->net.s2d.row_cells;
+  p.s2d_first_cell = e->net.s2d.pad2;
   dml::launch_preprocess(p, reinterpret_cast<const float*>(e->ws + e->off_lut), e->fp32, s);
   e->launches += 1;
   CUDA_TRY(cudaGetLastError());
@@ -358,7 +361,7 @@ int dml_create(int device, int model, int max_batch, int micro_batch, int flags,
   size_t off = 0;
   e->off_lut = off; off = align_up(off + 768 * 4, 256);
   e->s2d = e->use_tc && net.s2d.op >= 0 && getenv("DML_NO_S2D") == nullptr;
-  e->input_img_bytes = e->s2d ? (size_t)net.s2d.size * net.s2d.size * 16 * 2 : (size_t)net.input_size * net.input_size * 3 * e->act_bytes;
+  e->input_img_bytes = e->s2d ? (size_t)net.s2d.size * net.s2d.row_cells * 16 * 2 : (size_t)net.input_size * net.input_size * 3 * e->act_bytes;
   e->off_input = off; off = align_up(off + (size_t)max_batch * e->input_img_bytes + 64, 256);
   e->off_arena = off; off = align_up(off + (size_t)net.arena_elems * e->micro_batch * e->act_bytes, 256);
   e->off_pooled = off; off = align_up(off + (size_t)max_batch * net.tensors[net.pooled_tensor].c * 4, 256);
@@ -592,6 +595,14 @@ int dml_input_layout(dml_engine* e, int* layout, int* cells, int* cell_channels)
   *layout = e->s2d ? 1 : 0;
   if (cells) *cells = e->s2d ? e->net.s2d.size : e->net.input_size;
   if (cell_channels) *cell_channels = e->s2d ? 16 : 3;
+  return 0;
+}
+
+int dml_input_rows(dml_engine* e, int* row_cells, int* first_cell, int* swap_bit) {
+  if (!e) return fail(DML_EINVAL, "engine is NULL");
+  if (row_cells) *row_cells = e->s2d ? e->net.s2d.row_cells : e->net.input_size;
+  if (first_cell) *first_cell = e->s2d ? e->net.s2d.pad2 : 0;
+  if (swap_bit) *swap_bit = e->s2d ? 2 : -1;
   return 0;
 }
 

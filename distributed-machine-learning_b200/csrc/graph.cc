@@ -488,6 +488,7 @@ void plan_weights(Net* net, int wbytes, bool tc_pad) {
       net->s2d.size = (net->input_size + 1) / 2;
       net->s2d.k2 = a_max - a_min + 1;
       net->s2d.pad2 = -a_min;
+      net->s2d.row_cells = (int)align_up(net->s2d.size + net->s2d.k2 - 1, 8);
       net->s2d.w_off = off;
       off = align_up(off + (int64_t)st.cout * net->s2d.k2 * net->s2d.k2 * 16 * 2, 256);
     }

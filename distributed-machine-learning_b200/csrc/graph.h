@@ -99,6 +99,12 @@ struct Net {
     int op = -1;             // index of the stem op, -1 = none
     int size = 0;            // S2 = ceil(S / 2)
     int k2 = 0, pad2 = 0;
+    // Physical row of the space-to-depth input: pad2 zero cells, the S2 data cells, zero cells up to row_cells (a multiple of 8,
+    // >= S2 + k2 - 1).  With the horizontal padding in memory, a whole halo tile is ONE TMA box of 256-byte lines (8 cells) instead
+    // of one 32-byte line per cell -- the TMA unit's cost is per line -- and since 8 | row_cells the 32-byte swizzle of a cell's
+    // shared-memory row depends on its physical column only: K1 stores the cells already swizzled (the two 16-byte halves of the
+    // cells with bit 2 of the physical column set are swapped) and the TMA copies them without a swizzle of its own.
+    int row_cells = 0;
     int64_t w_off = 0;       // packed bf16 [cout][k2*k2][16], bytes into the weights buffer
   } s2d;
 };

@@ -130,9 +130,13 @@ __global__ void __launch_bounds__(256) preprocess_s2d_kernel(PreParams p, const 
       }
     }
   }
-  uint4* out = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + ((int64_t)img * S2 * S2 + rem) * 16);
-  out[0] = reinterpret_cast<uint4*>(vals)[0];
-  out[1] = reinterpret_cast<uint4*>(vals)[1];
+  // physical position: rows of s2d_row_cells cells, data cell x2 at column s2d_first_cell + x2; the 16-byte halves of a cell are
+  // swapped where bit 2 of the physical column is set (= the 32-byte swizzle of the shared-memory row the cell lands in)
+  const int xp = x2 + p.s2d_first_cell;
+  uint4* out = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (((int64_t)img * S2 + y2) * p.s2d_row_cells + xp) * 16);
+  const int sw = (xp >> 2) & 1;
+  out[sw] = reinterpret_cast<uint4*>(vals)[0];
+  out[sw ^ 1] = reinterpret_cast<uint4*>(vals)[1];
 }
 
 // ---------------------------------------------------------------------------

@@ -22,6 +22,9 @@ struct ConvParams {
   // the next layer starts, so the next layer begins with exactly those pixels instead of with the ones evicted long ago.
   int rev = 0;
   int norelu_cols = 0;  // output channels [0, norelu_cols) get no ReLU (graph.h, Op::norelu_cols); a multiple of 16
+  // Resident-filter halo kernel, 16-channel input (the space-to-depth stems): the input rows are physically padded to
+  // in_row_cells pixels (the left padding included) and pre-swizzled, graph.h Net::S2d::row_cells.  0 = plain NHWC.
+  int in_row_cells = 0;
   int in_img0 = 0;   // tcgen05 path: first image / first output row of this launch inside the
   int out_row0 = 0;  // planned tensor maps (the pointers above are already offset for the CUDA-core path)
 };
@@ -47,7 +50,9 @@ struct PreParams {
   int n, S;             // n = images in the tensor the tables cover
   int img_begin, img_end;  // images [img_begin, img_end) are produced by this launch
   int caffe;            // 1: output channel c reads source channel 2-c (RGB->BGR)
-  int s2d;              // 1: bf16 space-to-depth output [n][S2][S2][16], S2 = (S+1)/2 (graph.h, Net::S2d)
+  int s2d;              // 1: bf16 space-to-depth output [n][S2][row_cells][16], S2 = (S+1)/2 (graph.h, Net::S2d)
+  int s2d_row_cells;    // physical cells per row (row-padded, pre-swizzled form) and
+  int s2d_first_cell;   // the physical column of data cell 0
 };
 
 // K1: NEAREST resize (host-computed index tables) + preprocess LUT; bf16 or fp32 out.

@@ -320,9 +320,17 @@ class Engine:
         layout, cells, cch = C.c_int(), C.c_int(), C.c_int()
         _lib.check(self.l.dml_input_layout(self.h, C.byref(layout), C.byref(cells), C.byref(cch)))
         if layout.value == 1:
-            # space-to-depth cells [n][S2][S2][(py, px, c) + 4 zero channels] -> the [n][S][S][3] picture
+            # space-to-depth cells [n][S2][row_cells][(py, px, c) + 4 zero channels] -> the [n][S][S][3] picture; rows are padded
+            # (data cell x at column first + x) and cells whose physical column has bit `bit` set store their halves swapped
             s2 = cells.value
-            raw = self.workspace[off:off + n * s2 * s2 * 16 * 2].view(torch.bfloat16).view(n, s2, s2, 16)
+            rc, first, bit = C.c_int(), C.c_int(), C.c_int()
+            _lib.check(self.l.dml_input_rows(self.h, C.byref(rc), C.byref(first), C.byref(bit)))
+            rows = self.workspace[off:off + n * s2 * rc.value * 16 * 2].view(torch.bfloat16).view(n, s2, rc.value, 16)
+            cols = torch.arange(first.value, first.value + s2, device=rows.device)
+            raw = rows[:, :, first.value:first.value + s2, :]
+            if bit.value >= 0:
+                swapped = ((cols >> bit.value) & 1).bool().view(1, 1, s2, 1)
+                raw = torch.where(swapped, torch.cat([raw[..., 8:], raw[..., :8]], dim=-1), raw)
             pic = raw[..., :12].reshape(n, s2, s2, 2, 2, 3).permute(0, 1, 3, 2, 4, 5).reshape(n, 2 * s2, 2 * s2, 3)
             return pic[:, :self.size, :self.size].contiguous()
         nbytes = n * self.size * self.size * 3 * eb.value

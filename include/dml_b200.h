@@ -144,6 +144,13 @@ int dml_input_tensor(dml_engine* e, void** dev_ptr, int* elem_bytes);
  * the edge are zero -- the form in which the stride-2 stem convolution is a
  * stride-1 convolution.  cells = S or S2, cell_channels = 3 or 16. */
 int dml_input_layout(dml_engine* e, int* layout, int* cells, int* cell_channels);
+/* Physical rows of the layout-1 input tensor: every row holds row_cells cells (>= cells), data cell x sits at column
+ * first_cell + x and the other columns are zero (the stem's horizontal padding, kept in memory so that a whole halo tile
+ * is one TMA box); in the cells whose physical column has bit swap_bit set, the two 16-byte halves (channels 0..7 / 8..15)
+ * are stored swapped -- the shared-memory swizzle the tensor cores expect, applied when the cell is written.
+ * Layout 0: row_cells = cells, first_cell = 0, swap_bit = -1 (no swap).  Still the preprocess_input result of
+ * models.py:38 / :63, value for value. */
+int dml_input_rows(dml_engine* e, int* row_cells, int* first_cell, int* swap_bit);
 
 /* Logits (pre-softmax), n x 1000 fp32, valid after dml_forward / dml_infer. */
 int dml_logits(dml_engine* e, float** dev_ptr);
