@@ -346,6 +346,7 @@ __device__ long long g_tc2_prof[160 * 8];
 constexpr int OUT_BUF_BYTES = 4096;  // 32 rows x 128 B
 constexpr int OUT_STAGING_BYTES = 8 * 2 * OUT_BUF_BYTES;  // 8 epilogue warps x 2 buffers
 constexpr int TC2_THREADS = 320;                       // TMA warp, MMA warp, 8 epilogue warps
+constexpr int TC2X_THREADS = 352;                      // pair kernel: + one warp that loads the residual tiles
 
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
@@ -1271,7 +1272,7 @@ __device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & PEER_BIT_MASK) : "memory");
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2X_THREADS, 1)
     conv_tc2x_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                      const __grid_constant__ CUtensorMap map_o, const __grid_constant__ CUtensorMap map_r,
                      const __grid_constant__ CUtensorMap map_a2, const TcV2Params p) {
@@ -1343,17 +1344,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
       const int tix = p.rev ? total_tiles - 1 - tile : tile;
       const int mt = tix / p.n_tiles, nt = tix - mt * p.n_tiles;
       const int m0 = mt * 2 * BLOCK_M + (int)rank * BLOCK_M, n0 = nt * p.bn;
-      if (p.has_res == 1) {
-        const uint32_t rb = lt & 1u, rph = (lt >> 1) & 1u;
-        mbar_wait_spin(rempty0 + 8u * rb, rph ^ 1u);
-        if (elect_one()) {
-          mbar_arrive_expect_tx(rfull0 + 8u * rb, res_tile_bytes);
-          for (int c = 0, ci = 0; c < p.bn; c += p.cw, ++ci)
-            tma_load_2d(sR + rb * res_tile_bytes + (uint32_t)ci * chunk_bytes, &map_r, rfull0 + 8u * rb, n0 + c,
-                        p.out_row0 + m0);
-        }
-        __syncwarp();
-      }
       const int img = m0 / howo;
       const int rem = m0 - img * howo;
       const int oh = rem / p.wo, ow = rem - oh * p.wo;
@@ -1390,19 +1380,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
             cb = 0;
             if (++sx == p.kw) { sx = 0; ++r; }
           }
-        }
-      }
-      if (p.has_res == 2) {
-        // single residual buffer: chunk slot c is refilled as soon as the previous tile's epilogue has read it.  Issued
-        // after this tile's operand loads: the wait below depends on epilogue(t-1), which MMA(t+1) needs anyway.
-        const uint32_t rph = lt & 1u;
-        for (int c = 0, ci = 0; c < p.bn; c += p.cw, ++ci) {
-          mbar_wait_spin(rempty0 + 8u * ci, rph ^ 1u);
-          if (elect_one()) {
-            mbar_arrive_expect_tx(rfull0 + 8u * ci, chunk_bytes);
-            tma_load_2d(sR + (uint32_t)ci * chunk_bytes, &map_r, rfull0 + 8u * ci, n0 + c, p.out_row0 + m0);
-          }
-          __syncwarp();
         }
       }
     }
@@ -1469,6 +1446,40 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC2_THREADS, 1)
         g_tc2_prof[cluster_id * 8 + 3] = prof_full;
         g_tc2_prof[cluster_id * 8 + 4] = clock64() - prof_m0;
         g_tc2_prof[cluster_id * 8 + 7] = lt;
+      }
+    }
+  } else if (warp == 10) {
+    // ---------------- residual producer (both CTAs): its own warp, so that waiting for the epilogue to hand a residual slot
+    // back never holds up the operand stream of the next tile (with few k-blocks per tile the operand ring cannot run a whole
+    // tile ahead, and the MMA warp starved behind these waits) ----------------
+    if (p.has_res) {
+      const uint32_t chunk_bytes = (uint32_t)BLOCK_M * (uint32_t)p.cw * 2u;
+      uint32_t lt = 0;
+      for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++lt) {
+        const int tix = p.rev ? total_tiles - 1 - tile : tile;
+        const int mt = tix / p.n_tiles, nt = tix - mt * p.n_tiles;
+        const int m0 = mt * 2 * BLOCK_M + (int)rank * BLOCK_M, n0 = nt * p.bn;
+        if (p.has_res == 1) {
+          const uint32_t rb = lt & 1u, rph = (lt >> 1) & 1u;
+          mbar_wait_spin(rempty0 + 8u * rb, rph ^ 1u);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(rfull0 + 8u * rb, res_tile_bytes);
+            for (int c = 0, ci = 0; c < p.bn; c += p.cw, ++ci)
+              tma_load_2d(sR + rb * res_tile_bytes + (uint32_t)ci * chunk_bytes, &map_r, rfull0 + 8u * rb, n0 + c, p.out_row0 + m0);
+          }
+          __syncwarp();
+        } else {
+          // single residual buffer: chunk slot c is refilled as soon as the previous tile's epilogue has read it
+          const uint32_t rph = lt & 1u;
+          for (int c = 0, ci = 0; c < p.bn; c += p.cw, ++ci) {
+            mbar_wait_spin(rempty0 + 8u * ci, rph ^ 1u);
+            if (elect_one()) {
+              mbar_arrive_expect_tx(rfull0 + 8u * ci, chunk_bytes);
+              tma_load_2d(sR + (uint32_t)ci * chunk_bytes, &map_r, rfull0 + 8u * ci, n0 + c, p.out_row0 + m0);
+            }
+            __syncwarp();
+          }
+        }
       }
     }
   } else {
@@ -2732,7 +2743,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
       const int clusters = tiles < sm_limit / 2 ? tiles : sm_limit / 2;
       static const bool profx = getenv("DML_TC_PROF") != nullptr;
       k.prof = profx ? 1 : 0;
-      launch_pdl(conv_tc2x_kernel, dim3(2 * clusters), dim3(TC2_THREADS), op.smem, s, op.map_a, op.map_b, op.map_o, op.map_r, op.map_a2, k);
+      launch_pdl(conv_tc2x_kernel, dim3(2 * clusters), dim3(TC2X_THREADS), op.smem, s, op.map_a, op.map_b, op.map_o, op.map_r, op.map_a2, k);
       if (profx) {
         cudaStreamSynchronize(s);
         static long long h[160 * 8];

@@ -94,9 +94,17 @@ class Engine:
         _lib.check(self.l.dml_weights_ready(self.h))
 
     # -- hot path --------------------------------------------------------
+    def make_current(self):
+        """CUDA's current device is per THREAD: a task that runs in an executor thread starts on device 0, and the first
+        allocation or event there would build a context on GPU 0 from every worker process (1.7 s, once, per process --
+        measured on the 8-GPU job mix).  Every entry point that may be the first CUDA call of its thread selects the
+        engine's device first."""
+        _torch().cuda.set_device(self.device)
+
     def upload(self, hb: frontend.HostBatch):
         """Host->device copy of one HostBatch on the engine stream."""
         torch = _torch()
+        self.make_current()
         n = hb.n
         if n > self.max_batch:
             raise _lib.DmlError(f"batch of {n} exceeds max_batch {self.max_batch}")
@@ -178,6 +186,7 @@ class Engine:
         D2H of the top-5 on the compute stream.  Returns a ticket for collect().  At most two batches
         may be in flight; the H2D of a batch overlaps the kernels of the one before it."""
         torch = _torch()
+        self.make_current()
         if self._slots is None:
             self._make_slots()
         k = self._submitted % 2
@@ -237,6 +246,7 @@ class Engine:
         """Pinned host arrays of slot k (two slots): frontend.HostBatch(..., into=slot) fills them in place, so
         the H2D copies of submit() are asynchronous without a pin_memory() call per batch."""
         torch = _torch()
+        self.make_current()
         if self._host_slots is None:
             S, mb = self.size, self.max_batch
             self._host_slots = []

@@ -44,7 +44,8 @@ def _worker_main(index, device, inbox, acks, cfg):
         try:
             res = await models.perform_inference(model, files)
             n = len(res) if isinstance(res, dict) else 0
-            acks.put((index, task_id, "ok", time.perf_counter() - t_recv, n, res if cfg["return_results"] else None))
+            info = res if cfg["return_results"] else (("wall", cfg["_t_recv_wall"], time.time()) if cfg.get("timestamps") else None)
+            acks.put((index, task_id, "ok", time.perf_counter() - t_recv, n, info))
         except asyncio.CancelledError:
             acks.put((index, task_id, "cancelled", time.perf_counter() - t_recv, 0, None))
             raise
@@ -60,6 +61,7 @@ def _worker_main(index, device, inbox, acks, cfg):
                 break
             task_id, model, files = msg
             t_recv = time.perf_counter()
+            cfg["_t_recv_wall"] = time.time()
             if current is not None and not current.done():
                 current.cancel()  # worker.py:944-953: a new task request preempts the running task
                 try:
@@ -80,7 +82,7 @@ class GpuWorkerPool:
     """``devices``: one entry per worker (a device may appear more than once: several workers sharing a GPU)."""
 
     def __init__(self, devices, models=("ResNet50", "InceptionV3"), max_batch=72, decode_threads=None, warm_files=None,
-                 return_results=False, start_timeout=600.0):
+                 return_results=False, start_timeout=600.0, timestamps=False):
         self.devices = list(devices)
         n = len(self.devices)
         if decode_threads is None:
@@ -89,7 +91,8 @@ class GpuWorkerPool:
         self.acks = ctx.Queue()
         self.inboxes = [ctx.Queue() for _ in range(n)]
         cfg = {"models": tuple(models), "max_batch": int(max_batch), "decode_threads": int(decode_threads),
-               "warm_files": list(warm_files) if warm_files else None, "return_results": bool(return_results)}
+               "warm_files": list(warm_files) if warm_files else None, "return_results": bool(return_results),
+               "timestamps": bool(timestamps)}  # timestamps: acknowledgements carry (wall clock at receipt, at completion) for latency studies
         self.procs = [ctx.Process(target=_worker_main, args=(i, d, self.inboxes[i], self.acks, cfg), daemon=True)
                       for i, d in enumerate(self.devices)]
         for p in self.procs:
