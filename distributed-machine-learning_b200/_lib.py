@@ -86,6 +86,7 @@ _SIGS = {
     "dml_num_ops": [_vp, C.POINTER(_i)],
     "dml_op_info": [_vp, _i, C.c_char_p, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i64), C.POINTER(_i64),
                     C.POINTER(_i64)],
+    "dml_op_schedule": [_vp, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)],
     "dml_profile_forward": [_vp, _i, _vp, _vp, _vp, _i, _vp],
     "dml_conv2d_bf16": [_i, _vp, _vp, _vp, _vp, _vp] + [_i] * 17 + [_vp],
     "dml_chain_bf16": [_vp] * 11 + [_i, _i, _i, _vp],

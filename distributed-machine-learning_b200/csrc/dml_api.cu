@@ -87,6 +87,16 @@ struct dml_engine {
   bool s2d = false;          // K1 writes the space-to-depth input and the stem runs as a stride-1 halo conv (Net::S2d)
   size_t input_img_bytes = 0;
   dml::TcOpPlan stem_plan;
+  // Branch streams (graph.h, plan_streams): engine-owned side streams and one event per op another stream waits for.
+  bool branch_streams = false;
+  cudaStream_t side[7] = {};
+  cudaEvent_t join_ev[7] = {};
+  std::vector<cudaEvent_t> op_event;
+  ~dml_engine() {
+    for (cudaStream_t st : side) if (st) cudaStreamDestroy(st);
+    for (cudaEvent_t ev : join_ev) if (ev) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : op_event) if (ev) cudaEventDestroy(ev);
+  }
   // profiling (dml_profile_forward): one event pair per op launch
   bool profiling = false;
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof;
@@ -150,8 +160,26 @@ int plan_stem(dml_engine* e) {
   return 0;
 }
 
-int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
+// Streams and events of the branch schedule.  Measured on InceptionV3 batch 128 (B200): 47.2k -> 50.9k images/s.  The kernels
+// keep their full grids: capping the SMs of the convolutions that run side by side (equal caps of 50 / 75 %, or shares in
+// proportion to their measured times) lost 3 - 10 %, stream priorities changed nothing.
+int plan_branch_streams(dml_engine* e) {
   const dml::Net& net = e->net;
+  if (!e->branch_streams || net.n_streams < 2) return 0;
+  for (int k = 0; k + 1 < net.n_streams; ++k) {
+    if (!e->side[k]) CUDA_TRY(cudaStreamCreateWithFlags(&e->side[k], cudaStreamNonBlocking));
+    if (!e->join_ev[k]) CUDA_TRY(cudaEventCreateWithFlags(&e->join_ev[k], cudaEventDisableTiming));
+  }
+  e->op_event.resize(net.ops.size(), nullptr);
+  for (size_t i = 0; i < net.ops.size(); ++i)
+    if (net.ops[i].signal && !e->op_event[i]) CUDA_TRY(cudaEventCreateWithFlags(&e->op_event[i], cudaEventDisableTiming));
+  return 0;
+}
+
+int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s0) {
+  const dml::Net& net = e->net;
+  // Branch streams: per-op event timing needs the serial order, so profiling runs serially
+  const bool multi = e->branch_streams && net.n_streams > 1 && !e->profiling && !e->op_event.empty();
   // consecutive launches walk their tiles in opposite directions (kernels.h, ConvParams::rev): K1 ascending, the stem descending, ...
   static const bool pingpong = getenv("DML_NO_PINGPONG") == nullptr;
   int rev = 0;
@@ -163,6 +191,9 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
     const int cout_x = op.merged_cout > 0 ? op.merged_cout : op.cout;
     const dml::Tensor& ti = net.tensors[op.in];
     const dml::Tensor& to = net.tensors[out_t];
+    cudaStream_t s = multi && op.stream > 0 ? e->side[op.stream - 1] : s0;
+    if (multi)
+      for (int w : op.waits) CUDA_TRY(cudaStreamWaitEvent(s, e->op_event[w], 0));
     e->prof_begin((int)oi, s);
     if (pingpong) rev ^= 1;
     if (op.kind == dml::OP_CONV) {
@@ -227,7 +258,13 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s) {
       e->launches += 1;
     }
     e->prof_end(s);
+    if (multi && op.signal) CUDA_TRY(cudaEventRecord(e->op_event[oi], s));
   }
+  if (multi)  // every side stream joins the caller's stream: whatever follows (and the next call) sees the whole forward pass done
+    for (int k = 0; k + 1 < net.n_streams; ++k) {
+      CUDA_TRY(cudaEventRecord(e->join_ev[k], e->side[k]));
+      CUDA_TRY(cudaStreamWaitEvent(s0, e->join_ev[k], 0));
+    }
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -357,6 +394,10 @@ int dml_create(int device, int model, int max_batch, int micro_batch, int flags,
     delete e;
     return fail(DML_EINVAL, "%s", err.c_str());
   }
+  // independent branches of a block on their own streams (bf16 tensor-core engines; DML_BRANCH_STREAMS=0: serial order)
+  const char* bs = getenv("DML_BRANCH_STREAMS");
+  e->branch_streams = e->use_tc && !e->keep_all && !(bs && atoi(bs) == 0);
+  if (e->branch_streams) dml::plan_streams(&e->net, 4);
   const dml::Net& net = e->net;
   size_t off = 0;
   e->off_lut = off; off = align_up(off + 768 * 4, 256);
@@ -409,6 +450,7 @@ int dml_bind_workspace(dml_engine* e, void* dev_ptr, size_t bytes) {
     if (dml::tc_plan(&e->tc, e->net, e->ws, e->off_arena, e->off_input, e->off_tc, e->wts, e->micro_batch, e->max_batch) != 0)
       return fail(DML_ECUDA, "tcgen05 plan failed: %s", dml::tc_last_error());
     if (plan_stem(e) != 0) return DML_ECUDA;
+    if (int rc = plan_branch_streams(e)) return rc;
   }
   return 0;
 }
@@ -426,6 +468,7 @@ int dml_bind_weights(dml_engine* e, void* dev_ptr, size_t bytes) {
     if (dml::tc_plan(&e->tc, e->net, e->ws, e->off_arena, e->off_input, e->off_tc, e->wts, e->micro_batch, e->max_batch) != 0)
       return fail(DML_ECUDA, "tcgen05 plan failed: %s", dml::tc_last_error());
     if (plan_stem(e) != 0) return DML_ECUDA;
+    if (int rc = plan_branch_streams(e)) return rc;
   }
   return 0;
 }
@@ -616,6 +659,17 @@ int dml_logits(dml_engine* e, float** dev_ptr) {
 int dml_num_ops(dml_engine* e, int* n) {
   if (!e || !n) return fail(DML_EINVAL, "NULL argument");
   *n = (int)e->net.ops.size() + 2;
+  return 0;
+}
+
+int dml_op_schedule(dml_engine* e, int i, int* stream, int* num_waits, int* num_streams) {
+  if (!e) return fail(DML_EINVAL, "engine is NULL");
+  const dml::Net& net = e->net;
+  if (i < 0 || i >= (int)net.ops.size()) return fail(DML_EINVAL, "op index %d out of range", i);
+  const bool on = e->branch_streams && net.n_streams > 1;
+  if (stream) *stream = on ? net.ops[i].stream : 0;
+  if (num_waits) *num_waits = on ? (int)net.ops[i].waits.size() : 0;
+  if (num_streams) *num_streams = on ? net.n_streams : 1;
   return 0;
 }
 

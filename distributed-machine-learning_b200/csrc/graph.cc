@@ -341,6 +341,7 @@ void build_inception_v3(Builder& b) {
   for (int i = 0; i < 3; ++i) {  // mixed0..2, 35x35
     std::string n = "mixed" + std::to_string(i);
     const Tensor tx = net->tensors[x];
+    const int r0 = (int)net->ops.size();
     Builder::Head hd = b.head_begin(x, n, 64, 48, 64, 64 + 64 + 96 + pool_f[i], pool_f[i]);
     b.head_b1(x, hd);
     int t = b.head_red(x, hd, 0);
@@ -349,17 +350,20 @@ void build_inception_v3(Builder& b) {
     t = b.cb(t, -1, 96, 3, 3);
     b.cb(t, b.cat_view(hd, n + ":b3d", 128, 96), 96, 3, 3);
     b.pool_branch(x, hd, n, 224, pool_f[i]);
+    net->regions.push_back({r0, (int)net->ops.size() - 1});
     x = hd.cat;
   }
   {  // mixed3, 17x17
     const Tensor tx = net->tensors[x];
     int ho = (tx.h - 3) / 2 + 1;
+    const int r0 = (int)net->ops.size();
     int cat = b.new_tensor("mixed3", ho, ho, 384 + 96 + tx.c);
     b.cb(x, b.view(cat, "mixed3:b3", 0, 384), 384, 3, 3, false, 2);
     int t = b.cb(x, -1, 64, 1, 1);
     t = b.cb(t, -1, 96, 3, 3);
     b.cb(t, b.view(cat, "mixed3:b3d", 384, 96), 96, 3, 3, false, 2);
     b.pool(OP_MAXPOOL, x, b.view(cat, "mixed3:bp", 480, tx.c), "max_pooling2d_2", 3, 2, 0);
+    net->regions.push_back({r0, (int)net->ops.size() - 1});
     x = cat;
   }
   const int c7[4] = {128, 160, 160, 192};
@@ -367,6 +371,7 @@ void build_inception_v3(Builder& b) {
     std::string n = "mixed" + std::to_string(i + 4);
     const Tensor tx = net->tensors[x];
     int c = c7[i];
+    const int r0 = (int)net->ops.size();
     Builder::Head hd = b.head_begin(x, n, 192, c, c, 768, 192);
     b.head_b1(x, hd);
     int t = b.head_red(x, hd, 0);
@@ -378,11 +383,13 @@ void build_inception_v3(Builder& b) {
     t = b.cb(t, -1, c, 7, 1);
     b.cb(t, b.cat_view(hd, n + ":b7d", 384, 192), 192, 1, 7);
     b.pool_branch(x, hd, n, 576, 192);
+    net->regions.push_back({r0, (int)net->ops.size() - 1});
     x = hd.cat;
   }
   {  // mixed8, 8x8
     const Tensor tx = net->tensors[x];
     int ho = (tx.h - 3) / 2 + 1;
+    const int r0 = (int)net->ops.size();
     int cat = b.new_tensor("mixed8", ho, ho, 320 + 192 + tx.c);
     Builder::Pair pr = b.pair_begin(x, "mixed8:red", 192, 192);
     int t = b.red1(x, pr);
@@ -392,11 +399,13 @@ void build_inception_v3(Builder& b) {
     t = b.cb(t, -1, 192, 7, 1);
     b.cb(t, b.view(cat, "mixed8:b7x3", 320, 192), 192, 3, 3, false, 2);
     b.pool(OP_MAXPOOL, x, b.view(cat, "mixed8:bp", 512, tx.c), "max_pooling2d_3", 3, 2, 0);
+    net->regions.push_back({r0, (int)net->ops.size() - 1});
     x = cat;
   }
   for (int i = 9; i <= 10; ++i) {  // mixed9, mixed10, 8x8
     std::string n = "mixed" + std::to_string(i);
     const Tensor tx = net->tensors[x];
+    const int r0 = (int)net->ops.size();
     Builder::Head hd = b.head_begin(x, n, 320, 384, 448, 2048, 192);
     b.head_b1(x, hd);
     int t = b.head_red(x, hd, 0);
@@ -407,6 +416,7 @@ void build_inception_v3(Builder& b) {
     b.cb(t, b.cat_view(hd, n + ":bda", 1088, 384), 384, 1, 3);
     b.cb(t, b.cat_view(hd, n + ":bdb", 1472, 384), 384, 3, 1);
     b.pool_branch(x, hd, n, 1856, 192);
+    net->regions.push_back({r0, (int)net->ops.size() - 1});
     x = hd.cat;
   }
   b.head(x);
@@ -524,12 +534,129 @@ bool build(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut
   net->input_tensor = 0;
   if (model == 0) build_resnet50(b); else build_inception_v3(b);
   if (spec_only) return true;
+  for (size_t r = 0; r < net->regions.size(); ++r) {
+    const int f = net->regions[r].first, l = net->regions[r].second;
+    for (int i = f; i <= l; ++i) net->ops[i].region = (int)r;
+    for (Buf& bf : net->bufs)  // a branch's scratch must not alias another branch's: everything born in the block lives to its end
+      if (bf.first_use >= f && bf.first_use <= l && bf.last_use < l) bf.last_use = l;
+  }
   plan_arena(net, keep_all);
   plan_weights(net, wbytes, tc_pad);
   return true;
 }
 
 }  // namespace
+
+namespace {
+
+// One memory access of an op: a channel range of a buffer (arena address range for the aliasing test).
+struct Access {
+  int buf;          // >= 0: arena buffer; -1 input tensor; -2 pooled vector
+  int c0, c1;       // channels [c0, c1) of the buffer's pixel
+  int64_t a0, a1;   // per-image element range of the buffer inside the arena
+};
+
+Access access_of(const Net& net, int t, bool whole_blocks) {
+  const Tensor& tt = net.tensors[t];
+  Access a{tt.buf, tt.c_off, tt.c_off + tt.c, 0, 0};
+  if (whole_blocks) {  // tensor-core loaders fetch whole 64-channel blocks: the tail block may reach into the next slice
+    a.c1 = tt.c_off + (int)align_up(tt.c, 64);
+    if (a.c1 > tt.c_pitch) a.c1 = tt.c_pitch;
+  }
+  if (tt.buf >= 0) {
+    a.a0 = net.bufs[tt.buf].offset;
+    a.a1 = a.a0 + align_up(net.bufs[tt.buf].elems, 64);
+  }
+  return a;
+}
+
+bool conflicts(const Access& x, const Access& y) {
+  if (x.buf < 0 || y.buf < 0) return x.buf == y.buf;
+  if (x.buf == y.buf) return x.c0 < y.c1 && y.c0 < x.c1;
+  return x.a0 < y.a1 && y.a0 < x.a1;  // two buffers the arena placed on the same addresses
+}
+
+}  // namespace
+
+void plan_streams(Net* net, int max_streams) {
+  const int n = (int)net->ops.size();
+  for (Op& op : net->ops) { op.stream = 0; op.signal = false; op.solo = true; op.waits.clear(); }
+  net->n_streams = 1;
+  if (net->regions.empty() || max_streams < 2) return;
+  if (max_streams > 8) max_streams = 8;
+  std::vector<std::vector<Access>> rd(n), wr(n);
+  std::vector<int> exec;  // ops that launch something, in serial order
+  for (int i = 0; i < n; ++i) {
+    const Op& op = net->ops[i];
+    if (op.skip) continue;  // computed by its leader, whose accesses cover it
+    exec.push_back(i);
+    rd[i].push_back(access_of(*net, op.in, op.kind == OP_CONV));
+    if (op.res >= 0) rd[i].push_back(access_of(*net, op.res, false));
+    if (op.in2 >= 0) rd[i].push_back(access_of(*net, op.in2, true));
+    wr[i].push_back(access_of(*net, op.merged_out >= 0 ? op.merged_out : op.out, false));
+  }
+  // hazards (read-after-write, write-after-read, write-after-write) and their transitive closure
+  std::vector<std::vector<int>> deps(n);
+  std::vector<std::vector<char>> anc(n, std::vector<char>(n, 0));
+  for (size_t xi = 0; xi < exec.size(); ++xi) {
+    const int i = exec[xi];
+    for (size_t xj = 0; xj < xi; ++xj) {
+      const int j = exec[xj];
+      bool hz = false;
+      for (const Access& w : wr[j]) {
+        for (const Access& r : rd[i]) hz = hz || conflicts(w, r);
+        for (const Access& w2 : wr[i]) hz = hz || conflicts(w, w2);
+      }
+      for (const Access& r : rd[j])
+        for (const Access& w2 : wr[i]) hz = hz || conflicts(r, w2);
+      if (!hz) continue;
+      deps[i].push_back(j);
+      anc[i][j] = 1;
+      for (int k = 0; k < n; ++k) anc[i][k] = anc[i][k] | anc[j][k];
+    }
+  }
+  std::vector<int> tail(max_streams, -1);
+  int used = 1;
+  for (int i : exec) {
+    Op& op = net->ops[i];
+    int k = -1;
+    if (tail[0] < 0) k = 0;
+    for (int d : deps[i])  // continue the chain of a direct producer (the caller's stream first)
+      if (k < 0 && tail[0] == d) k = 0;
+    if (k < 0) {
+      int best = -1;
+      for (int q = 1; q < max_streams; ++q)
+        for (int d : deps[i])
+          if (tail[q] == d && d > best) { best = d; k = q; }
+    }
+    if (k < 0)  // a stream that has nothing this op could overlap with: empty, or its last op is an ancestor
+      for (int q = 0; q < max_streams && k < 0; ++q)
+        if (tail[q] < 0 || anc[i][tail[q]]) k = q;
+    if (k < 0) {  // all streams busy with independent work: queue behind the one whose last op is the oldest
+      k = 0;
+      for (int q = 1; q < max_streams; ++q)
+        if (tail[q] < tail[k]) k = q;
+    }
+    op.stream = k;
+    if (k + 1 > used) used = k + 1;
+    for (int d : deps[i]) {
+      if (net->ops[d].stream == k) continue;  // stream order
+      bool covered = tail[k] >= 0 && anc[tail[k]][d];  // already ordered before this stream's previous op
+      for (int d2 : deps[i]) covered = covered || (d2 != d && anc[d2][d]);
+      if (covered) continue;
+      op.waits.push_back(d);
+      net->ops[d].signal = true;
+    }
+    tail[k] = i;
+  }
+  net->n_streams = used;
+  for (int i : exec) {
+    Op& op = net->ops[i];
+    if (op.region < 0) continue;
+    for (int j : exec)
+      if (j != i && net->ops[j].region == op.region && !anc[i][j] && !anc[j][i]) op.solo = false;
+  }
+}
 
 bool build_net(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut, Net* net, std::string* err, bool pool_commute) {
   return build(model, keep_all, wbytes, tc_pad, fuse_shortcut, false, net, err, pool_commute);

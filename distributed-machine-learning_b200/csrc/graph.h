@@ -5,6 +5,7 @@
 #pragma once
 #include <cstdint>
 #include <string>
+#include <utility>
 #include <vector>
 
 namespace dml {
@@ -72,6 +73,13 @@ struct Op {
   int norelu_cols = 0;
   int pool_bias_of = -1;
   int in2 = -1, cin2 = 0, cin2_pad = 0, stride2 = 1;
+  // Branch streams (plan_streams): independent branches of an InceptionV3 block run on different CUDA streams.  stream 0 is
+  // the caller's; before its launch the op waits for the events of the ops in `waits` (producers / memory hazards on other
+  // streams); `signal`: some op on another stream waits for this one.  region: index into Net::regions (-1 outside the
+  // blocks); solo: every other op of the region is an ancestor or a descendant (the block's head GEMM), so it runs alone.
+  int stream = 0, region = -1;
+  bool signal = false, solo = true;
+  std::vector<int> waits;
   int w2_kernel = -1, w2_bias = -1, w2_gamma = -1, w2_beta = -1, w2_mean = -1, w2_var = -1;
   float eps2 = 0.f;
 };
@@ -92,6 +100,10 @@ struct Net {
   int64_t arena_elems = 0;             // per image
   int64_t weights_bytes = 0;
   int64_t conv_macs = 0;               // per image
+  // Blocks whose branches may run concurrently: [first op, last op].  Buffers first touched inside a region stay live to its
+  // end, so the arena never makes one branch's scratch alias another's.  n_streams: streams plan_streams() used (1 = serial).
+  std::vector<std::pair<int, int>> regions;
+  int n_streams = 1;
   // Space-to-depth form of the C_in = 3 stride-2 stem (bf16 tensor-core mode only): the S x S x 3 input is stored as
   // S2 x S2 x 16 (channel (py*2+px)*3 + c = pixel (2y+py, 2x+px), channels 12..15 zero) and the k x k stride-2 filter
   // becomes a k2 x k2 stride-1 filter over it whose first tap sits pad2 cells before the output position.
@@ -115,6 +127,11 @@ struct Net {
 // fuse_shortcut: ResNet50's projection shortcuts become a second GEMM source of the block's last conv (Op::in2) and
 // InceptionV3's sibling 1x1 branch heads become one GEMM (Op::followers).
 bool build_net(int model, bool keep_all, int wbytes, bool tc_pad, bool fuse_shortcut, Net* net, std::string* err, bool pool_commute = true);
+
+// Assigns the ops of a net with regions to at most max_streams streams (Op::stream / waits / signal / solo) from the true
+// data dependencies plus every memory hazard the arena plan creates.  Serial order on one stream is always a valid schedule;
+// this only relaxes it.
+void plan_streams(Net* net, int max_streams);
 
 // Only the weight-array list (cheap; for dml_model_* queries).
 bool build_weight_spec(int model, Net* net, std::string* err);

@@ -396,6 +396,16 @@ class Engine:
             out.append((buf.value.decode(), k.value, im.value, macs.value, ab.value, wb.value))
         return out
 
+    def schedule(self):
+        """[(name, stream, num_waits)] per layer-plan op and the number of streams in use (dml_op_schedule)."""
+        ops = self.ops()
+        out, ns = [], C.c_int(1)
+        for i, o in enumerate(ops[:-2]):  # the dense and softmax ops always run on the caller's stream
+            st, nw = C.c_int(), C.c_int()
+            _lib.check(self.l.dml_op_schedule(self.h, i, C.byref(st), C.byref(nw), C.byref(ns)))
+            out.append((o[0], st.value, nw.value))
+        return out, ns.value
+
     def profile_forward(self, n: int):
         """Per-op milliseconds of one forward over the current input tensor (CUDA events around each launch)."""
         nops = len(self.ops())

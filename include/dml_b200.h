@@ -163,6 +163,13 @@ int dml_num_ops(dml_engine* e, int* n);
 int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* impl, int64_t* macs_per_img,
                 int64_t* act_bytes_per_img, int64_t* weight_bytes);
 
+/* Branch schedule of op i (0 <= i < dml_num_ops minus the two head ops): independent branches of an InceptionV3 block
+ * (the Keras functional graph behind /root/reference/models.py:26 runs them in whatever order TensorFlow's executor picks) are
+ * launched on engine-owned CUDA streams that fork from and join the stream passed to dml_forward / dml_infer.  stream: 0 = the
+ * caller's stream; num_waits: events of other streams the op waits for; num_streams: streams in use (1 = serial: ResNet50, the
+ * fp32 check mode, DML_BRANCH_STREAMS=0).  Results do not depend on it. */
+int dml_op_schedule(dml_engine* e, int i, int* stream, int* num_waits, int* num_streams);
+
 /* dml_forward with a CUDA-event pair around every launch: op_ms[i] receives the
  * milliseconds op i took, summed over the micro-batches (cap >= dml_num_ops).
  * Synchronous; for bench.py's roofline, not for production. */
