@@ -2019,6 +2019,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc5_kernel(const __grid_co
 }
 
 #include "conv_chain.inc"
+#include "conv_duo.inc"
 
 }  // namespace
 
@@ -2101,6 +2102,9 @@ int tc_init() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_chain_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_duo_kernel) failed: %s", cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc3_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc2x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
@@ -2940,6 +2944,122 @@ int launch_chain(const ChainPlan& pl, const ChainArgs& a, cudaStream_t s) {
   return 0;
 }
 
+// ---- conv_duo_kernel: plan + launch over explicit pointers ----
+bool duo_supported(const DuoArgs& a) {
+  if (a.M <= 0 || !a.y2 || !a.we || !a.be || !a.res || !a.out || !a.wr || !a.br || !a.y1n) return false;
+  if (a.kmid % 64 || a.kmid < 64 || a.kmid > 256) return false;
+  if (a.nexp % 256 || a.nexp < 256 || a.nexp > 2048) return false;
+  if (a.nred % 64 || a.nred < 64 || a.nred > 256) return false;
+  if (a.y2_pitch % 8 || a.out_pitch % 8 || a.res_pitch % 8 || a.y1n_pitch % 16) return false;
+  if (reinterpret_cast<uintptr_t>(a.y1n) % 32) return false;  // 32-byte vector stores per pixel
+  return true;
+}
+
+int duo_plan(DuoPlan* out, const DuoArgs& a, int m_capacity) {
+  if (!g_encode_tiled) return tc_fail("tc_init was not called");
+  if (!duo_supported(a)) return tc_fail("shape is not eligible for the expand + reduce kernel");
+  DuoPlan pl;
+  const int kmb = a.kmid / 64, nj = a.nexp / 64;
+  // Buffering, best first: eight `out` slots (twice the residual / store traffic in flight; the ring of slots is what bounds the
+  // kernel), a second y2 tile (the next tile's GEMM2 starts without waiting for its load), then weight stages.
+  const int opts[9][4] = {{8, 2, 2, 2}, {8, 1, 3, 3}, {8, 1, 2, 2}, {4, 2, 4, 4}, {4, 2, 3, 2}, {4, 2, 2, 2}, {4, 1, 4, 3}, {4, 1, 3, 2}, {4, 1, 2, 2}};
+  static const int slots_env = getenv("DML_DUO_SLOTS") ? atoi(getenv("DML_DUO_SLOTS")) : 8;  // experiments: 4 = never more than four slots
+  bool fit = false;
+  for (const auto& o : opts) {
+    if (o[0] > slots_env) continue;
+    const DuoSmem L = duo_smem(kmb, nj, a.nred, o[1], o[2], o[3], o[0]);
+    if (L.total <= (uint32_t)SMEM_LIMIT) {
+      pl.slots = o[0]; pl.y2_bufs = o[1]; pl.we_stages = o[2]; pl.wr_stages = o[3]; pl.smem = L.total;
+      fit = true;
+      break;
+    }
+  }
+  if (!fit) return tc_fail("expand + reduce kernel does not fit in shared memory (kmid %d, nexp %d, nred %d)", a.kmid, a.nexp, a.nred);
+  pl.m_capacity = m_capacity;
+  auto map2d = [&](CUtensorMap* m, const void* base, int cols, int rows, int pitch, int box_rows, bool weights) -> CUresult {
+    cuuint64_t d[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t st[1] = {(cuuint64_t)pitch * 2};
+    cuuint32_t b[2] = {64u, (cuuint32_t)box_rows};
+    cuuint32_t es[2] = {1, 1};
+    return g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), d, st, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, weights ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  };
+  CUresult r;
+  if ((r = map2d(&pl.map_y2, a.y2, a.kmid, m_capacity, a.y2_pitch, BLOCK_M, false)) != CUDA_SUCCESS) return tc_fail("duo: y2 map failed (%d)", (int)r);
+  if ((r = map2d(&pl.map_we, a.we, a.kmid, a.nexp, a.kmid, 32, true)) != CUDA_SUCCESS) return tc_fail("duo: expand weight map failed (%d)", (int)r);
+  if ((r = map2d(&pl.map_wr, a.wr, a.nexp, a.nred, a.nexp, a.nred / 2, true)) != CUDA_SUCCESS) return tc_fail("duo: reduce weight map failed (%d)", (int)r);
+  if ((r = map2d(&pl.map_res, a.res, a.nexp, m_capacity, a.res_pitch, BLOCK_M, false)) != CUDA_SUCCESS) return tc_fail("duo: residual map failed (%d)", (int)r);
+  if ((r = map2d(&pl.map_out, a.out, a.nexp, m_capacity, a.out_pitch, 16, false)) != CUDA_SUCCESS) return tc_fail("duo: output map failed (%d)", (int)r);
+  pl.valid = true;
+  *out = pl;
+  return 0;
+}
+
+int launch_duo(const DuoPlan& pl, const DuoArgs& a, cudaStream_t s) {
+  if (!pl.valid) return tc_fail("duo plan is not valid");
+  if (a.M > pl.m_capacity) return tc_fail("%d pixels exceed the planned capacity %d", a.M, pl.m_capacity);
+  DuoParams k{};
+  k.bias2 = a.be; k.bias3 = a.br;
+  k.y1n = reinterpret_cast<__nv_bfloat16*>(a.y1n); k.y1n_pitch = a.y1n_pitch;
+  k.M = a.M; k.m_tiles = (a.M + 2 * BLOCK_M - 1) / (2 * BLOCK_M);
+  k.kmb = a.kmid / 64; k.nj = a.nexp / 64; k.nred = a.nred;
+  k.y2_bufs = pl.y2_bufs; k.we_stages = pl.we_stages; k.wr_stages = pl.wr_stages; k.ns = pl.slots;
+  k.rev = a.rev;
+  static const int pf_env = getenv("DML_DUO_PF") ? atoi(getenv("DML_DUO_PF")) : 8;
+  k.pf = pf_env;
+  static const bool prof = getenv("DML_CHAIN_PROF") != nullptr;
+  if (prof) {
+    static long long zero[160 * 40] = {};
+    cudaMemcpyToSymbol(g_chain_prof, zero, sizeof zero);
+  }
+  const int pairs = g_num_sms / 2;
+  const int clusters = k.m_tiles < pairs ? k.m_tiles : pairs;
+  static const bool dbg = getenv("DML_CHAIN_DEBUG") != nullptr;  // debugging aid shared with the chain kernel (wait ids are 64 + barrier index here)
+  static unsigned long long* h_word = nullptr;
+  if (dbg && !h_word) {
+    unsigned long long* d_word = nullptr;
+    if (cudaHostAlloc(&h_word, sizeof *h_word, cudaHostAllocMapped) == cudaSuccess && cudaHostGetDevicePointer(&d_word, h_word, 0) == cudaSuccess) {
+      *h_word = 0;
+      cudaMemcpyToSymbol(g_chain_dbg_ptr, &d_word, sizeof d_word);
+    }
+  }
+  if (prof) launch_pdl(conv_duo_kernel<true>, dim3(2 * clusters), dim3(DUO_THREADS), pl.smem, s, pl.map_y2, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, k);
+  else launch_pdl(conv_duo_kernel<false>, dim3(2 * clusters), dim3(DUO_THREADS), pl.smem, s, pl.map_y2, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, k);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return tc_fail("conv_duo_kernel launch: %s", cudaGetErrorString(e));
+  if (prof) {
+    cudaStreamSynchronize(s);
+    static long long h[160 * 40];
+    cudaMemcpyFromSymbol(h, g_chain_prof, sizeof h);
+    double v[40] = {};
+    double nt = 0, loop = 0, ntl = 0;
+    for (int b = 0; b < 2 * clusters && b < 160; ++b) {
+      for (int i = 0; i < 38; ++i) v[i] += (double)h[b * 40 + i];
+      nt += (double)h[b * 40 + 39];
+      if (b % 2 == 0) { loop += (double)h[b * 40 + 38]; ntl += (double)h[b * 40 + 39]; }
+    }
+    if (nt < 1) nt = 1;
+    const char* names[18] = {"g2:y2_full", "res:y2_empty", "g2:we_full", "g3:wr_full", "B|w:acc2_full", "g2:acc2_empty", "B:res_full", "g3:outc_full",
+                             "res|w:outc_empty", "res:slot_free", "A:acc3_full", "g3:acc3_empty", "B:compute", "B:store", "g2:issue", "g2:commit",
+                             "g3:issue", "g3:commit"};
+    fprintf(stderr, "[duo prof] kmid %d nexp %d, %d slots, y2 x%d, stages %d/%d: %.1f tiles per cluster, %.0f cycles per tile | cycles per tile and CTA (one warp per role; the issuers' are per pair: double them):", a.kmid, a.nexp,
+            pl.slots, pl.y2_bufs, pl.we_stages, pl.wr_stages, ntl / clusters, loop / (ntl > 0 ? ntl : 1));
+    for (int i = 0; i < 18; ++i)
+      if (v[i] > 0) fprintf(stderr, " %s %.0f", names[i], v[i] / nt);
+    fprintf(stderr, "\n");
+  }
+  if (dbg) {
+    cudaError_t se = cudaStreamSynchronize(s);
+    fprintf(stderr, "[duo debug] launch (M %d, kmid %d, nexp %d, nred %d, y2 bufs %d, stages %d/%d): sync -> %s, word %llx\n", a.M, a.kmid, a.nexp, a.nred,
+            pl.y2_bufs, pl.we_stages, pl.wr_stages, cudaGetErrorString(se), h_word ? *h_word : 0ull);
+    if (h_word && *h_word)
+      fprintf(stderr, "[duo debug] wait id %llu timed out at index %llu, block %llu, warp %llu (%s)\n", *h_word & 0xff, (*h_word >> 8) & 0xffff,
+              (*h_word >> 24) & 0xffff, (*h_word >> 40) & 0xff, cudaGetErrorString(se));
+  }
+  return 0;
+}
+
 namespace {
 // milliseconds of one launch, or a huge number if the candidate cannot run: one warm-up, then the best of
 // three bursts of four launches (the first bursts after an idle period run at ramping clocks)
@@ -2975,7 +3095,7 @@ static std::map<std::string, std::vector<TuneChoice>> g_tune_cache;
 
 static std::string tune_key(const Net& net, int micro_batch) {
   char buf[160];
-  snprintf(buf, sizeof buf, "v3_m%d_mb%d_ops%zu_sm%d_w%lld", net.model, micro_batch, net.ops.size(), g_num_sms, (long long)net.weights_bytes);
+  snprintf(buf, sizeof buf, "v4_m%d_mb%d_ops%zu_sm%d_w%lld", net.model, micro_batch, net.ops.size(), g_num_sms, (long long)net.weights_bytes);
   return buf;
 }
 static std::string tune_file(const std::string& key) {
@@ -3047,6 +3167,21 @@ static void chain_args(const Net& net, uint8_t* wts, int lead, int n, PtrFn ptr,
     a->y1n = ptr(orr.out); a->y1n_pitch = net.tensors[orr.out].c_pitch;
   }
   a->n = n; a->h = ty1.h; a->w = ty1.w;
+}
+
+template <class PtrFn>
+static void duo_args(const Net& net, uint8_t* wts, int lead, int n, PtrFn ptr, DuoArgs* a) {
+  const Op& oe = net.ops[lead];
+  const Op& orr = net.ops[oe.duo_red];
+  const Tensor& ty2 = net.tensors[oe.in];
+  a->y2 = ptr(oe.in); a->y2_pitch = ty2.c_pitch;
+  a->we = wts + oe.wpack_off; a->be = reinterpret_cast<const float*>(wts + oe.bias_off);
+  a->res = ptr(oe.res); a->res_pitch = net.tensors[oe.res].c_pitch;
+  a->out = ptr(oe.out); a->out_pitch = net.tensors[oe.out].c_pitch;
+  a->wr = wts + orr.wpack_off; a->br = reinterpret_cast<const float*>(wts + orr.bias_off);
+  a->y1n = ptr(orr.out); a->y1n_pitch = net.tensors[orr.out].c_pitch;
+  a->M = n * ty2.h * ty2.w;
+  a->kmid = oe.cin; a->nexp = oe.cout; a->nred = orr.cout;
 }
 
 int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t off_input, size_t off_tc, uint8_t* wts,
@@ -3220,6 +3355,53 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
       if (o3.chain_red >= 0) plan->chained[o3.chain_red] = 1;
     }
   }
+  // ---- expand + next reduce duos (conv_duo.inc): fused kernel against the two separate ones ----
+  plan->duos.assign(net.ops.size(), DuoPlan());
+  if (!getenv("DML_NO_DUO")) {
+    auto tptr = [&](int t) -> uint8_t* {
+      const Tensor& tt = net.tensors[t];
+      return ws + off_arena + ((size_t)net.bufs[tt.buf].offset * micro_batch + tt.c_off) * 2;
+    };
+    for (size_t i = 0; i < net.ops.size(); ++i) {
+      const Op& oe = net.ops[i];
+      if (oe.duo_red < 0 || plan->chained[i] || plan->chained[oe.duo_red]) continue;
+      if (net.tensors[oe.in].buf < 0 || !plan->ops[i].valid || !plan->ops[oe.duo_red].valid || oe.cin_pad != oe.cin) continue;
+      DuoArgs a;
+      duo_args(net, wts, (int)i, micro_batch, tptr, &a);
+      DuoPlan dp;
+      if (duo_plan(&dp, a, a.M) != 0) {
+        if (tune_log) fprintf(stderr, "[tune] duo at %s not planned: %s\n", oe.name.c_str(), tc_last_error());
+        continue;
+      }
+      bool use = true;
+      if (have_cache && cached[i].chain >= 0) {
+        use = cached[i].chain == 1;
+        chosen[i].chain = cached[i].chain;
+      } else if (autotune && !over_budget) {
+        float best = 1e30f;
+        if (launch_duo(dp, a, nullptr) != 0 || cudaDeviceSynchronize() != cudaSuccess) return tc_fail("duo kernel failed at %s: %s", oe.name.c_str(), cudaGetErrorString(cudaGetLastError()));
+        for (int rep = 0; rep < 3; ++rep) {
+          cudaEventRecord(ev0, nullptr);
+          for (int k = 0; k < 4; ++k) launch_duo(dp, a, nullptr);
+          cudaEventRecord(ev1, nullptr);
+          if (cudaEventSynchronize(ev1) != cudaSuccess) return tc_fail("duo kernel failed at %s: %s", oe.name.c_str(), cudaGetErrorString(cudaGetLastError()));
+          float ms = 0.f;
+          cudaEventElapsedTime(&ms, ev0, ev1);
+          if (ms / 4.f < best) best = ms / 4.f;
+        }
+        dp.ms = best;
+        dp.ms_separate = plan->ops[i].best_ms + plan->ops[oe.duo_red].best_ms;
+        use = dp.ms < dp.ms_separate || getenv("DML_FORCE_DUO");
+        if (tune_log)
+          fprintf(stderr, "[tune] duo %s + %s: fused %.4f ms, separate %.4f ms -> %s\n", oe.name.c_str(), net.ops[oe.duo_red].name.c_str(), dp.ms,
+                  dp.ms_separate, use ? "fused" : "separate");
+        chosen[i].chain = use ? 1 : 0;
+      }
+      if (!use) continue;
+      plan->duos[i] = dp;
+      plan->chained[oe.duo_red] = 1;
+    }
+  }
   if (autotune && !have_cache && !over_budget) tune_store(key, chosen);
   if (autotune) {
     cudaEventDestroy(ev0);
@@ -3239,6 +3421,18 @@ int launch_chain_tc(const TcPlan& plan, const Net& net, uint8_t* wts, int lead, 
   chain_args(net, wts, lead, n, tptr, &a);
   a.rev = rev;
   return launch_chain(plan.chains[lead], a, s);
+}
+
+int launch_duo_tc(const TcPlan& plan, const Net& net, uint8_t* wts, int lead, int n, uint8_t* ws, size_t off_arena, cudaStream_t s, int rev) {
+  if (lead < 0 || lead >= (int)plan.duos.size() || !plan.duos[lead].valid) return tc_fail("no duo plan for op %d", lead);
+  auto tptr = [&](int t) -> uint8_t* {
+    const Tensor& tt = net.tensors[t];
+    return ws + off_arena + ((size_t)net.bufs[tt.buf].offset * plan.micro_batch + tt.c_off) * 2;
+  };
+  DuoArgs a;
+  duo_args(net, wts, lead, n, tptr, &a);
+  a.rev = rev;
+  return launch_duo(plan.duos[lead], a, s);
 }
 
 int launch_conv_tc(const TcPlan& plan, int op_index, const ConvParams& p, int img0, cudaStream_t s, int* nlaunch) {

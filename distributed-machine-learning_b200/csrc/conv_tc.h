@@ -67,8 +67,33 @@ bool chain_supported(const ChainArgs& a);
 int chain_plan(ChainPlan* out, const ChainArgs& a, int n_capacity);
 int launch_chain(const ChainPlan& plan, const ChainArgs& a, cudaStream_t s);
 
+// A 1x1 expand (+ residual) and the next block's 1x1 reduce as one kernel (conv_duo.inc; ResNet50 conv3 / conv4).
+struct DuoArgs {
+  const void* y2 = nullptr; int y2_pitch = 0;      // input of the expand: [M][kmid] bf16 (pitch in elements)
+  const void* we = nullptr; const float* be = nullptr;   // packed [nexp][kmid], folded bias
+  const void* res = nullptr; int res_pitch = 0;    // residual [M][nexp]
+  void* out = nullptr; int out_pitch = 0;          // block output [M][nexp]
+  const void* wr = nullptr; const float* br = nullptr;   // next block's reduce: packed [nred][nexp], folded bias
+  void* y1n = nullptr; int y1n_pitch = 0;          // its output [M][nred]
+  int M = 0;                                       // pixels (n * h * w)
+  int kmid = 0, nexp = 0, nred = 0;
+  int rev = 0;  // ConvParams::rev
+};
+struct DuoPlan {
+  bool valid = false;
+  alignas(64) CUtensorMap map_y2, map_we, map_wr, map_res, map_out;
+  int y2_bufs = 1, we_stages = 2, wr_stages = 2, slots = 4;
+  size_t smem = 0;
+  int m_capacity = 0;
+  float ms = 0.f, ms_separate = 0.f;  // autotune: this kernel against the two separate ones
+};
+bool duo_supported(const DuoArgs& a);
+int duo_plan(DuoPlan* out, const DuoArgs& a, int m_capacity);
+int launch_duo(const DuoPlan& plan, const DuoArgs& a, cudaStream_t s);
+
 struct TcPlan {
   std::vector<TcOpPlan> ops;  // indexed like Net::ops
+  std::vector<DuoPlan> duos;  // indexed like Net::ops; valid at the expand that leads a duo the engine runs fused
   std::vector<ChainPlan> chains;  // indexed like Net::ops; valid at the 3x3 that leads a chain the engine runs fused
   std::vector<char> chained;      // op is computed inside a valid chain's launch
   int micro_batch = 0;
@@ -94,6 +119,8 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
 int launch_conv_tc(const TcPlan& plan, int op_index, const ConvParams& p, int img0, cudaStream_t s, int* nlaunch);
 // Runs the fused chain led by op `lead` (plan.chains[lead].valid) over the first n images of the arena.
 int launch_chain_tc(const TcPlan& plan, const Net& net, uint8_t* wts, int lead, int n, uint8_t* ws, size_t off_arena, cudaStream_t s, int rev = 0);
+// Runs the fused expand + next reduce led by op `lead` (plan.duos[lead].valid) over the first n images of the arena.
+int launch_duo_tc(const TcPlan& plan, const Net& net, uint8_t* wts, int lead, int n, uint8_t* ws, size_t off_arena, cudaStream_t s, int rev = 0);
 const char* tc_last_error();
 // Tiled bf16 tensor map (rank <= 5) for kernels outside conv_tc.cu; swizzle_bytes in {0, 32, 64, 128}.
 int tc_make_tiled_map(CUtensorMap* out, void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,

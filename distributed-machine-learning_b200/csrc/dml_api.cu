@@ -220,6 +220,11 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s0) {
         if (dml::launch_chain_tc(e->tc, net, e->wts, (int)oi, cnt, e->ws, e->off_arena, s, rev) != 0)
           return fail(DML_ECUDA, "chain kernel launch failed at %s: %s", op.name.c_str(), dml::tc_last_error());
         nl = 1;
+      } else if (e->use_tc && oi < e->tc.duos.size() && e->tc.duos[oi].valid) {
+        // 1x1 expand + residual + the next block's reduce as one kernel
+        if (dml::launch_duo_tc(e->tc, net, e->wts, (int)oi, cnt, e->ws, e->off_arena, s, rev) != 0)
+          return fail(DML_ECUDA, "expand + reduce kernel launch failed at %s: %s", op.name.c_str(), dml::tc_last_error());
+        nl = 1;
       } else if (e->s2d && (int)oi == net.s2d.op) {
         dml::ConvParams p2 = stem_s2d_params(e, img0, cnt);
         p2.rev = rev;
@@ -729,6 +734,14 @@ int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* 
           ab += px * orr.cout * 2;
         }
       }
+      if (e->use_tc && (size_t)i < e->tc.duos.size() && e->tc.duos[i].valid) {
+        // fused duo: this launch also does the next block's reduce; the re-read of `out` never reaches HBM
+        const dml::Op& orr = net.ops[op.duo_red];
+        const int64_t px = (int64_t)to.h * to.w;
+        macs += px * orr.cout * orr.cin;
+        wb += (int64_t)orr.cout * orr.cin * 2 + orr.cout * 4;
+        ab += px * orr.cout * 2;
+      }
     }
   }
   if (name && name_cap > 0) snprintf(name, name_cap, "%s", nm.c_str());
@@ -827,6 +840,23 @@ int dml_chain_bf16(const void* d_y1, const void* d_w3, const float* d_b3, const 
   dml::ChainPlan plan;
   if (dml::chain_plan(&plan, a, n) != 0) return fail(DML_EINVAL, "%s", dml::tc_last_error());
   if (dml::launch_chain(plan, a, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
+  return 0;
+}
+
+int dml_duo_bf16(const void* d_y2, const void* d_we, const float* d_be, const void* d_res, void* d_out, const void* d_wr,
+                 const float* d_br, void* d_y1n, int m, int kmid, int nexp, int nred, void* stream) {
+  if (m < 1) return fail(DML_EINVAL, "m must be positive");
+  if (dml::tc_init() != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
+  dml::DuoArgs a;
+  a.y2 = d_y2; a.y2_pitch = kmid;
+  a.we = d_we; a.be = d_be;
+  a.res = d_res; a.res_pitch = nexp;
+  a.out = d_out; a.out_pitch = nexp;
+  a.wr = d_wr; a.br = d_br; a.y1n = d_y1n; a.y1n_pitch = nred;
+  a.M = m; a.kmid = kmid; a.nexp = nexp; a.nred = nred;
+  dml::DuoPlan plan;
+  if (dml::duo_plan(&plan, a, m) != 0) return fail(DML_EINVAL, "%s", dml::tc_last_error());
+  if (dml::launch_duo(plan, a, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
   return 0;
 }
 

@@ -321,6 +321,25 @@ void build_resnet50(Builder& b) {
       }
     }
   }
+  if (b.fuse_shortcut) {
+    // conv3 / conv4: an identity-residual block's 1x1 expand and the following block's 1x1 reduce may run as one kernel
+    for (int oi = 0; oi + 1 < (int)net->ops.size(); ++oi) {
+      Op& oe = net->ops[oi];
+      Op& orr = net->ops[oi + 1];
+      if (oe.kind != OP_CONV || oe.kh != 1 || oe.kw != 1 || oe.stride != 1 || oe.res < 0 || oe.in2 >= 0 || !oe.relu) continue;
+      if (oe.chain_lead >= 0 || (oe.cin != 128 && oe.cin != 256) || oe.cout != 4 * oe.cin) continue;
+      if (orr.kind != OP_CONV || orr.kh != 1 || orr.kw != 1 || orr.stride != 1 || orr.in != oe.out || orr.cin != oe.cout ||
+          orr.cout != oe.cin || !orr.relu || orr.res >= 0 || orr.in2 >= 0)
+        continue;
+      oe.duo_red = oi + 1;
+      orr.duo_lead = oi;
+      for (int k = oi; k <= oi + 1; ++k) {  // one launch reads and writes all of these
+        const Op& m = net->ops[k];
+        for (int t : {m.in, m.out, m.res})
+          if (t >= 0) { b.touch(t, oi); b.touch(t, oi + 1); }
+      }
+    }
+  }
   b.head(x);
 }
 

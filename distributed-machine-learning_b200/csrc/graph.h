@@ -63,6 +63,9 @@ struct Op {
   // 1x1 expand (chain_exp) and the next block's 1x1 reduce (chain_red, -1 for the stage's last block); chain_lead on
   // the members points back.  The engine decides at plan time whether the fused kernel or the separate ones run.
   int chain_exp = -1, chain_red = -1, chain_lead = -1;
+  // Expand + next reduce duo (ResNet50 conv3 / conv4, conv_duo.inc): on a 1x1 expand with an identity residual, duo_red is
+  // the next block's 1x1 reduce the engine may compute in the same launch; duo_lead on that reduce points back.
+  int duo_red = -1, duo_lead = -1;
   // InceptionV3's pool branch is AveragePooling2D -> 1x1 conv -> BN -> ReLU.  The pool and the 1x1 conv are both linear and act
   // on different axes (space / channels), so they commute: relu(conv(avgpool(x)) + b) == relu(avgpool(conv(x)) + b).  In fused
   // engines the conv (post_pool = true) joins the block's merged head GEMM WITHOUT bias and ReLU (its output channels come first

@@ -141,6 +141,7 @@ def test_engine_with_and_without_the_chain_gives_the_same_bits(images, monkeypat
         monkeypatch.delenv("DML_NO_CHAIN", raising=False)
         monkeypatch.delenv("DML_FORCE_CHAIN", raising=False)
         monkeypatch.setenv("DML_FORCE_CHAIN" if chain else "DML_NO_CHAIN", "1")
+        monkeypatch.setenv("DML_NO_DUO", "1")  # (the conv3 / conv4 duos have their own test)
         eng = pkg("engine").Engine("ResNet50", max_batch=40, weights=W)
         try:
             names = [o[0] for o in eng.ops() if o[1] == 0 and o[3] == 0]  # convs that report no work of their own: chain members
