@@ -45,7 +45,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not _stale():
         return LIB_PATH
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-o", LIB_PATH] + [os.path.join(CSRC, f) for f in SOURCES] + ["-ldl"]
+    # DML_B200_LEGACY_VARIANTS=1: also compile the superseded kernel variants (impl 1, 3, 4 of dml_conv2d_bf16), the A/B twins
+    # the surviving kernels were checked against; the product library does not carry them
+    extra = ["-DDML_LEGACY_VARIANTS"] if os.environ.get("DML_B200_LEGACY_VARIANTS") == "1" else []
+    cmd = [nvcc] + NVCC_FLAGS + extra + ["-o", LIB_PATH] + [os.path.join(CSRC, f) for f in SOURCES] + ["-ldl"]
     if verbose:
         print(" ".join(cmd))
     r = subprocess.run(cmd, capture_output=True, text=True)
@@ -56,6 +59,11 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 _lib = None
 _lock = threading.Lock()
+
+
+def has_legacy_variants() -> bool:
+    """True when the loaded library was built with -DDML_LEGACY_VARIANTS (dml_conv2d_bf16 impl 1, 3, 4)."""
+    return b"legacy" in lib().dml_version()
 
 _vp, _i, _i64, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_size_t
 _SIGS = {

@@ -177,6 +177,7 @@ __device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t (&v)[1
       : "memory");
 }
 
+#ifdef DML_LEGACY_VARIANTS  // superseded A/B twins (one tile per CTA; halo kernel with streamed weights): test builds only
 // ------------------------------- the kernel --------------------------------
 __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                              const __grid_constant__ CUtensorMap map_b,
@@ -309,6 +310,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv_tc_kernel(const __grid_consta
 }
 
 
+#endif  // DML_LEGACY_VARIANTS
 // ------------------- v2: persistent, warp-specialised kernel -------------------
 // One CTA per SM walks tiles tile = blockIdx.x + i*gridDim.x (N tiles of one M tile
 // adjacent, so concurrent CTAs share the A rows in L2).  The smem ring and the
@@ -627,6 +629,11 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) conv_tc2_kernel(const __grid_c
 }
 
 
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+#ifdef DML_LEGACY_VARIANTS
 // ------------- v3: stride-1 multi-tap convs with the input halo staged ONCE -------------
 // im2col through L2 re-reads every input pixel once per filter tap (9x for 3x3) and the
 // L2 -> SM path (~6 TB/s, no faster than HBM) is what bounds those layers.  Here a tile is
@@ -647,10 +654,6 @@ struct TcV3Params {
   int tmem_cols, acc_stride, cw;
   int in_img0, out_img0;
 };
-
-__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
-}
 
 
 __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_constant__ CUtensorMap map_a,
@@ -865,6 +868,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc3_kernel(const __grid_co
 }
 
 
+#endif  // DML_LEGACY_VARIANTS
 // ------------- v6: halo kernel with the WHOLE filter resident in shared memory -------------
 // For stride-1 multi-tap layers with few channels (ResNet50 conv2 3x3, the InceptionV3 stem 3x3s) one
 // tcgen05.mma is short (N <= 96) and the issuing warp cannot hide a barrier round trip behind it
@@ -2080,8 +2084,13 @@ int tc_init() {
     g_encode_im2col = reinterpret_cast<PFN_cuTensorMapEncodeIm2col>(fn);
     cudaDriverGetVersion(&g_driver_version);
   }
-  cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  cudaError_t e = cudaSuccess;
+#ifdef DML_LEGACY_VARIANTS
+  e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
+  e = cudaFuncSetAttribute(conv_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc3_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
+#endif
   e = cudaFuncSetAttribute(conv_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc5_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaSuccess;
@@ -2105,8 +2114,6 @@ int tc_init() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_duo_kernel) failed: %s", cudaGetErrorString(e));
-  e = cudaFuncSetAttribute(conv_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
-  if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc3_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc2x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc2x_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
@@ -2137,6 +2144,10 @@ int tc_make_tiled_map(CUtensorMap* out, void* base, int rank, const uint64_t* di
 
 int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune& tune) {
   if (!g_encode_tiled) return tc_fail("tc_init was not called");
+#ifndef DML_LEGACY_VARIANTS
+  if (tune.version == 1 || tune.version == 3)
+    return tc_fail("kernel variant %d is a superseded A/B twin: not in this build (compile with -DDML_LEGACY_VARIANTS)", tune.version);
+#endif
   TcOpPlan op;
   // ---- v5: weights as the A operand, 256 pixels per instruction (Cout <= 128, no residual) ----
   if (tune.version == 5) {
@@ -2692,6 +2703,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     if (e6 != cudaSuccess) return tc_fail("conv_tc6_kernel launch: %s", cudaGetErrorString(e6));
     return 0;
   }
+#ifdef DML_LEGACY_VARIANTS
   if (op.version == 3) {
     TcV3Params k{};
     k.bias = p.bias;
@@ -2711,6 +2723,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     if (e3 != cudaSuccess) return tc_fail("conv_tc3_kernel launch: %s", cudaGetErrorString(e3));
     return 0;
   }
+#endif
   if (op.version == 2 || op.version == 4) {
     const bool pair = op.version == 4;
     TcV2Params k{};
@@ -2777,6 +2790,9 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     if (e2 != cudaSuccess) return tc_fail("conv_tc2_kernel launch: %s", cudaGetErrorString(e2));
     return 0;
   }
+#ifndef DML_LEGACY_VARIANTS
+  return tc_fail("kernel variant %d is not in this build (compile with -DDML_LEGACY_VARIANTS)", op.version);
+#else
   TcKernelParams k{};
   k.bias = p.bias;
   k.res = reinterpret_cast<const __nv_bfloat16*>(p.res);
@@ -2792,6 +2808,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return tc_fail("conv_tc_kernel launch: %s", cudaGetErrorString(e));
   return 0;
+#endif
 }
 
 

@@ -328,7 +328,13 @@ extern "C" {
 int dml_set_error(int code, const char* msg) { return fail(code, "%s", msg); }
 
 const char* dml_last_error(void) { return g_err.c_str(); }
-const char* dml_version(void) { return "dml_b200 0.1 (sm_100a)"; }
+const char* dml_version(void) {
+#ifdef DML_LEGACY_VARIANTS
+  return "dml_b200 0.1 (sm_100a) +legacy-variants";
+#else
+  return "dml_b200 0.1 (sm_100a)";
+#endif
+}
 
 int dml_model_info(int model, int* input_size, int* preprocess_mode) {
   if (int rc = check_model(model)) return rc;
@@ -810,6 +816,9 @@ int dml_conv2d_bf16(int impl, const void* d_in, const void* d_w, const float* d_
     return 0;
   }
   if (impl == 3) {
+#ifndef DML_LEGACY_VARIANTS
+    return fail(DML_EINVAL, "impl 3 (the patch-expanding C=3 stem kernel) is a superseded A/B twin: not in this build (compile with -DDML_LEGACY_VARIANTS)");
+#endif
     if (!dml::stem_tc_supported(p)) return fail(DML_EINVAL, "shape is not a C_in = 3 stride-2 stem convolution");
     if (dml::launch_stem_tc(p, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "stem conv launch failed");
     return 0;

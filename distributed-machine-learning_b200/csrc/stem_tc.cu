@@ -17,6 +17,14 @@
 #include "conv_tc.h"
 #include "kernels.h"
 
+// Superseded by the space-to-depth stem (the stem as a stride-1 halo convolution, conv_tc6_kernel): kept as an A/B twin in
+// test builds (-DDML_LEGACY_VARIANTS); the product library carries stubs only.
+#ifndef DML_LEGACY_VARIANTS
+namespace dml {
+bool stem_tc_supported(const ConvParams&) { return false; }
+int launch_stem_tc(const ConvParams&, cudaStream_t) { return -1; }
+}  // namespace dml
+#else
 namespace dml {
 namespace {
 
@@ -359,3 +367,4 @@ int launch_stem_tc(const ConvParams& c, cudaStream_t s) {
 }
 
 }  // namespace dml
+#endif  // DML_LEGACY_VARIANTS

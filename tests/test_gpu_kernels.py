@@ -143,9 +143,17 @@ def test_conv_cuda_core_vs_torch(shape):
         assert (out[..., cout:].float() == 7.0).all()  # neighbours of the channel slice untouched
 
 
+def _need_legacy():
+    """impl 1 / 3 / 4 are superseded A/B twins: only in libraries built with DML_B200_LEGACY_VARIANTS=1 (csrc: -DDML_LEGACY_VARIANTS)."""
+    if not pkg("_lib").has_legacy_variants():
+        pytest.skip("superseded kernel variant: not in the product build (DML_B200_LEGACY_VARIANTS=1 builds it)")
+
+
 @pytest.mark.parametrize("impl", [1, 2], ids=["tile_per_cta", "persistent"])
 @pytest.mark.parametrize("shape", CONV_SHAPES, ids=lambda s: "x".join(map(str, s[:10])))
 def test_conv_tcgen05_vs_cuda_core_and_torch(shape, impl):
+    if impl == 1:
+        _need_legacy()
     rng = np.random.default_rng(hash(shape) % 2**32)
     case = _conv_case(rng, *shape)
     base = _run_conv(0, case)
@@ -193,6 +201,7 @@ def test_conv_tcgen05_persistent_tiles(case_id):
 @pytest.mark.parametrize("shape", [(3, 224, 224, 3, 64, 7, 7, 2, 3, 3, True, False), (2, 299, 299, 3, 32, 3, 3, 2, 0, 0, True, False),
                                    (1, 37, 53, 3, 64, 7, 7, 2, 3, 3, True, False)], ids=["resnet", "inception", "ragged"])
 def test_stem_conv_tcgen05(shape):
+    _need_legacy()
     rng = np.random.default_rng(99)
     case = _conv_case(rng, *shape, cin_pad=3)
     ref = case["ref"]
@@ -221,6 +230,7 @@ HALO_CASES = [
 
 @pytest.mark.parametrize("case_id", range(len(HALO_CASES)))
 def test_conv_tcgen05_halo_kernel(case_id):
+    _need_legacy()
     shape, tile_n, stages = HALO_CASES[case_id]
     rng = np.random.default_rng(4321 + case_id)
     case = _conv_case(rng, *shape)
@@ -341,10 +351,12 @@ def test_conv_tcgen05_variants_are_bit_identical():
         big = 128 if shape[4] % 128 == 0 else 96
         g = lambda k, stages=0: (k << 8) | stages   # k-blocks per pipeline stage ride in bits 8..15 of `stages`
         outs = [_run_conv(2, case, 0, 0), _run_conv(2, case, 64, 2), _run_conv(2, case, big, 0), _run_conv(5, case, 0, 0),
-                _run_conv(5, case, 64, 3), _run_conv(1, case, 0, 0), _run_conv(2, case, 64, g(1)), _run_conv(2, case, 64, g(4)),
+                _run_conv(5, case, 64, 3), _run_conv(2, case, 64, g(1)), _run_conv(2, case, 64, g(4)),
                 _run_conv(2, case, 32, g(5, 2)), _run_conv(5, case, 64, g(1)), _run_conv(5, case, 64, g(3)),
                 _run_conv(5, case, big, g(2, 2)), _run_conv(5, case, 32, g(7)),
                 _run_conv(5, case, 0, 1 << 16), _run_conv(5, case, 0, 2 << 16), _run_conv(5, case, 64, (2 << 16) | g(2))]  # residual paths
+        if pkg("_lib").has_legacy_variants():
+            outs.append(_run_conv(1, case, 0, 0))
         for o in outs[1:]:
             assert torch.equal(o, outs[0])
 
