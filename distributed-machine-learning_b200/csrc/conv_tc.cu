@@ -1832,7 +1832,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC6_THREADS, 1)
 }
 
 
-#define DML_V6X_SHAPES(X) X(3, 3, 1, 128) X(3, 3, 2, 128) X(5, 5, 1, 128) X(1, 7, 2, 128) X(7, 1, 2, 128) X(1, 7, 3, 128) X(7, 1, 3, 128)
+#define DML_V6X_SHAPES(X) X(3, 3, 1, 128) X(3, 3, 2, 128) X(5, 5, 1, 128) X(1, 7, 2, 128) X(7, 1, 2, 128) X(1, 7, 3, 128) X(7, 1, 3, 128) \
+    X(3, 3, 3, 64) X(1, 7, 5, 64) X(7, 1, 5, 64)
 
 // ------------- v5: "weights as A" for layers with few output channels -------------
 // A tcgen05.mma takes ~190 cycles on B200 whatever its N (measured), so with pixels on M (128 per
@@ -2100,7 +2101,8 @@ int tc_init() {
 #undef DML_V6X_ATTR
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc6x_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
 #define DML_V6_SHAPES_INIT(X) X(3, 3, 1, 128) X(3, 3, 1, 64) X(3, 3, 2, 128) X(4, 4, 1, 32) X(2, 2, 1, 32) X(5, 5, 1, 128) \
-    X(1, 7, 2, 128) X(7, 1, 2, 128) X(1, 7, 3, 128) X(7, 1, 3, 128) X(1, 3, 6, 128) X(3, 1, 6, 128) X(0, 0, 0, 0)
+    X(1, 7, 2, 128) X(7, 1, 2, 128) X(1, 7, 3, 128) X(7, 1, 3, 128) X(1, 3, 6, 128) X(3, 1, 6, 128) X(3, 3, 3, 64) X(1, 7, 5, 64) X(7, 1, 5, 64) \
+    X(0, 0, 0, 0)
   e = cudaSuccess;
 #define DML_V6_ATTR(KH_, KW_, CB_, RB_) \
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6_kernel<KH_, KW_, CB_, RB_>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
@@ -2212,7 +2214,8 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
   // ---- v6x (version 7): the resident-filter halo kernel on CTA pairs, row-aligned tiles ----
   if (tune.version == 7) {
     const int wp = p.wo + p.kw - 1;
-    const int row_bytes = p.cin <= 16 ? 32 : (p.cin <= 32 ? 64 : 128);
+    // K blocks of 32 channels (64-byte rows) on request: Cin = 80 / 96 / 160 pad to 96 / 96 / 160 channels instead of 128 / 128 / 192
+    const int row_bytes = p.cin <= 16 ? 32 : ((p.cin <= 32 || tune.row_bytes == 64) ? 64 : 128);
     const int kb = row_bytes / 2;
     const int cblocks = (p.cin + kb - 1) / kb;
     const int taps = p.kh * p.kw;
@@ -2275,7 +2278,8 @@ int tc_plan_one(TcOpPlan* out, const ConvParams& p, int n_capacity, const TcTune
     if (p.in_row_cells && (p.cin != 16 || p.in_pitch != 16 || p.in_row_cells % 8 || p.in_row_cells < p.wo + p.kw - 1 || p.in_row_cells > 256 * 8))
       return tc_fail("row-padded input needs 16 channels and a row of a multiple of 8 pixels that covers the padded width");
     const int wp = p.in_row_cells ? p.in_row_cells : p.wo + p.kw - 1;
-    const int row_bytes = p.cin <= 16 ? 32 : (p.cin <= 32 ? 64 : 128);
+    // K blocks of 32 channels (64-byte rows) on request: Cin = 80 / 96 / 160 pad to 96 / 96 / 160 channels instead of 128 / 128 / 192
+    const int row_bytes = p.cin <= 16 ? 32 : ((p.cin <= 32 || tune.row_bytes == 64) ? 64 : 128);
     const int kb = row_bytes / 2;
     const int cblocks = (p.cin + kb - 1) / kb;
     const int taps = p.kh * p.kw;
@@ -2679,7 +2683,7 @@ int launch_conv_tc_plan(const TcOpPlan& op, const ConvParams& p, cudaStream_t s)
     k.prof = prof6 ? 1 : 0;
     // compile-time shapes (fully unrolled MMA issue); anything else takes the generic loop
 #define DML_V6_SHAPES(X) X(3, 3, 1, 128) X(3, 3, 1, 64) X(3, 3, 2, 128) X(4, 4, 1, 32) X(2, 2, 1, 32) X(5, 5, 1, 128) \
-    X(1, 7, 2, 128) X(7, 1, 2, 128) X(1, 7, 3, 128) X(7, 1, 3, 128) X(1, 3, 6, 128) X(3, 1, 6, 128)
+    X(1, 7, 2, 128) X(7, 1, 2, 128) X(1, 7, 3, 128) X(7, 1, 3, 128) X(1, 3, 6, 128) X(3, 1, 6, 128) X(3, 3, 3, 64) X(1, 7, 5, 64) X(7, 1, 5, 64)
     bool launched = false;
 #define DML_V6_TRY(KH_, KW_, CB_, RB_)                                                                                         \
     if (!launched && p.kh == KH_ && p.kw == KW_ && op.cpb == CB_ && op.row_bytes == RB_) {                                       \
@@ -3106,13 +3110,14 @@ float time_plan(const TcOpPlan& op, const ConvParams& p, cudaEvent_t e0, cudaEve
 // bounded by DML_TUNE_BUDGET_MS of wall time (default 30000): ops past the budget keep the heuristic plan.
 struct TuneChoice {
   int version = 0, bn = 0, group = 0, res_direct = 0, chain = -1;  // chain: -1 not a chain lead, 0 separate, 1 fused
+  int row_bytes = 0;
   float ms = 0.f;
 };
 static std::map<std::string, std::vector<TuneChoice>> g_tune_cache;
 
 static std::string tune_key(const Net& net, int micro_batch) {
   char buf[160];
-  snprintf(buf, sizeof buf, "v4_m%d_mb%d_ops%zu_sm%d_w%lld", net.model, micro_batch, net.ops.size(), g_num_sms, (long long)net.weights_bytes);
+  snprintf(buf, sizeof buf, "v5_m%d_mb%d_ops%zu_sm%d_w%lld", net.model, micro_batch, net.ops.size(), g_num_sms, (long long)net.weights_bytes);
   return buf;
 }
 static std::string tune_file(const std::string& key) {
@@ -3141,7 +3146,7 @@ static bool tune_load(const std::string& key, size_t nops, std::vector<TuneChoic
   std::vector<TuneChoice> v(nops);
   size_t n = 0, idx;
   TuneChoice c;
-  while (f >> idx >> c.version >> c.bn >> c.group >> c.res_direct >> c.chain >> c.ms) {
+  while (f >> idx >> c.version >> c.bn >> c.group >> c.res_direct >> c.chain >> c.row_bytes >> c.ms) {
     if (idx >= nops) return false;
     v[idx] = c;
     ++n;
@@ -3160,7 +3165,7 @@ static void tune_store(const std::string& key, const std::vector<TuneChoice>& v)
     std::ofstream f(tmp);
     if (!f) return;
     for (size_t i = 0; i < v.size(); ++i)
-      f << i << ' ' << v[i].version << ' ' << v[i].bn << ' ' << v[i].group << ' ' << v[i].res_direct << ' ' << v[i].chain << ' ' << v[i].ms << '\n';
+      f << i << ' ' << v[i].version << ' ' << v[i].bn << ' ' << v[i].group << ' ' << v[i].res_direct << ' ' << v[i].chain << ' ' << v[i].row_bytes << ' ' << v[i].ms << '\n';
   }
   rename(tmp.c_str(), fn.c_str());  // atomic: concurrent ranks write the same table
 }
@@ -3251,6 +3256,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     if (have_cache && cached[i].version != 0) {
       TcTune t;
       t.version = cached[i].version; t.bn = cached[i].bn; t.group = cached[i].group; t.res_direct = cached[i].res_direct;
+      t.row_bytes = cached[i].version >= 6 && cached[i].row_bytes == 64 ? 64 : 0;
       if (tc_plan_one(&plan->ops[i], p, micro_batch, t) == 0 && plan->ops[i].version == cached[i].version && plan->ops[i].bn == cached[i].bn) {
         plan->ops[i].best_ms = cached[i].ms;
         chosen[i] = cached[i];
@@ -3275,8 +3281,8 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     float best = time_plan(plan->ops[i], p, ev0, ev1);
     const float first = best;
     // candidates: kernel variant x N tile x k-blocks per stage (v2 / v4); duplicates of an already timed plan are skipped
-    std::vector<std::array<int, 3>> seen;
-    seen.push_back({plan->ops[i].version, plan->ops[i].bn, plan->ops[i].group});
+    std::vector<std::array<int, 4>> seen;
+    seen.push_back({plan->ops[i].version, plan->ops[i].bn, plan->ops[i].group, plan->ops[i].row_bytes});
     for (int version : {4, 2, 5, 6, 7}) {
       if (op.in2 >= 0 && version != 4) continue;  // only the pair kernel reads a second GEMM source
       if (op.norelu_cols > 0 && version != 4 && version != 2) continue;  // ReLU-free leading columns: persistent GEMM kernels only
@@ -3284,19 +3290,20 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
         if (version == 5 && (bn != 0 || cout_x > 128 || op.res >= 0)) continue;
         if (version == 6 && bn != 0) continue;
         if (bn && (cout_x % bn != 0 || bn > cout_x)) continue;
-        for (int g : {0, 1, 2, 3, 4}) {
-          if (version >= 5 && g != 0) continue;
+        for (int g : {0, 1, 2, 3, 4, 64}) {  // 64: the halo kernels with 64-byte rows (32-channel K blocks) where that pads Cin less
+          if (version >= 5 && g != 0 && g != 64) continue;
+          if (g == 64 && (version < 6 || op.cin <= 32 || (op.cin + 31) / 32 * 32 >= (op.cin + 63) / 64 * 64)) continue;
           TcTune t;
-          t.version = version; t.bn = bn; t.group = g;
+          t.version = version; t.bn = bn; t.group = g == 64 ? 0 : g; t.row_bytes = g == 64 ? 64 : 0;
           TcOpPlan cand;
           if (tc_plan_one(&cand, p, micro_batch, t) != 0) continue;
-          const std::array<int, 3> key = {cand.version, cand.bn, cand.group};
+          const std::array<int, 4> key = {cand.version, cand.bn, cand.group, cand.row_bytes};
           bool dup = false;
           for (const auto& k : seen) dup = dup || k == key;
           if (dup) continue;
           seen.push_back(key);
           float ms = time_plan(cand, p, ev0, ev1);
-          if (tune_log) fprintf(stderr, "[tune]   %s v%d bn %d group %d stages %d: %.4f ms\n", op.name.c_str(), cand.version, cand.bn, cand.group, cand.stages, ms);
+          if (tune_log) fprintf(stderr, "[tune]   %s v%d bn %d group %d stages %d row %d: %.4f ms\n", op.name.c_str(), cand.version, cand.bn, cand.group, cand.stages, cand.row_bytes, ms);
           if (ms < best * 0.98f) { best = ms; plan->ops[i] = cand; }
         }
       }
@@ -3315,6 +3322,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
     }
     plan->ops[i].best_ms = best;
     chosen[i].version = plan->ops[i].version; chosen[i].bn = plan->ops[i].bn; chosen[i].group = plan->ops[i].group;
+    chosen[i].row_bytes = plan->ops[i].row_bytes;
     chosen[i].res_direct = plan->ops[i].has_res ? (plan->ops[i].res_direct ? 2 : 1) : 0; chosen[i].ms = best;
     if (tune_log)
       fprintf(stderr, "[tune] %s -> v%d bn %d group %d stages %d: %.4f ms (heuristic %.4f)\n", op.name.c_str(), plan->ops[i].version,

@@ -104,6 +104,7 @@ struct TcTune {
   int bn = 0;
   int stages = 0;
   int group = 0;    // k-blocks per pipeline stage for v2 / v4 (0 = heuristic)
+  int row_bytes = 0;   // halo kernels (v6 / v7): bytes of a shared-memory pixel row = 2 x channels per K block; 0 = by Cin (<= 16: 32, <= 32: 64, else 128)
   int res_direct = 0;  // v4 residual staging: 0 = heuristic, 1 = two tile buffers, 2 = one buffer, chunks handed back one by one
   int version = 0;  // 1 = one tile per CTA, 2 = persistent im2col, 3 = halo kernel, 4 = CTA-pair (cta_group::2) persistent, 5 = weights as A, 6 = halo kernel with the filter resident in shared memory, 7 = the same on CTA pairs; 0 = choose
 };

@@ -827,7 +827,7 @@ int dml_conv2d_bf16(int impl, const void* d_in, const void* d_w, const float* d_
   if (dml::tc_init() != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
   dml::TcOpPlan plan;
   dml::TcTune tune;
-  tune.bn = tile_n; tune.stages = stages & 0xff; tune.group = (stages >> 8) & 0xff; tune.res_direct = (stages >> 16) & 3; tune.version = impl == 4 ? 3 : (impl == 5 ? 4 : (impl == 6 ? 5 : (impl == 7 ? 6 : (impl == 8 ? 7 : impl))));  // 5 = CTA-pair kernel, 6 = weights-as-A kernel, 7 = resident-filter halo kernel, 8 = the same on CTA pairs
+  tune.bn = tile_n; tune.stages = stages & 0xff; tune.group = (stages >> 8) & 0xff; tune.res_direct = (stages >> 16) & 3; tune.row_bytes = ((stages >> 18) & 1) ? 64 : 0; tune.version = impl == 4 ? 3 : (impl == 5 ? 4 : (impl == 6 ? 5 : (impl == 7 ? 6 : (impl == 8 ? 7 : impl))));  // 5 = CTA-pair kernel, 6 = weights-as-A kernel, 7 = resident-filter halo kernel, 8 = the same on CTA pairs
   if (dml::tc_plan_one(&plan, p, n, tune) != 0) return fail(DML_EINVAL, "%s", dml::tc_last_error());
   if (dml::launch_conv_tc_plan(plan, p, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
   return 0;

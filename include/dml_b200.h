@@ -188,7 +188,10 @@ int dml_launch_count(dml_engine* e, int64_t* launches);
  * with the filter resident in shared memory, 8 = the same on CTA pairs (the engine
  * picks per layer among 2, 5, 6, 7, 8); tile_n / stages: 0 = default;
  * bits 8..15 of `stages` = 64-channel k-blocks per pipeline stage for impl 2 / 5 (0 = default),
- * bits 16..17 = residual staging of impl 5 (0 default, 1 two tile buffers, 2 one buffer with per-chunk hand-back).
+ * bits 16..17 = residual staging of impl 5 (0 default, 1 two tile buffers, 2 one buffer with per-chunk hand-back),
+ * bit 18 = impl 7 / 8 with 32-channel K blocks (64-byte shared-memory rows) whatever Cin.
+ * impl 1, 3, 4 are superseded A/B twins: only in libraries compiled with -DDML_LEGACY_VARIANTS (dml_version() then
+ * ends in "+legacy-variants"); otherwise they return DML_EINVAL.
  * The unit-test and tuning hook for the convolution kernels. */
 int dml_conv2d_bf16(int impl, const void* d_in, const void* d_w, const float* d_bias, const void* d_res, void* d_out,
                     int n, int hi, int wi, int cin, int in_pitch, int cout, int out_pitch, int res_pitch, int kh,

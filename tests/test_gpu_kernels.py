@@ -341,6 +341,40 @@ def test_conv_tcgen05_pair_resident_filter_halo(shape):
     assert torch.equal(out, _run_conv(2, case))   # same bits as the im2col kernel
 
 
+NARROW_ROW_CASES = [
+    # Cin that 32-channel K blocks (64-byte shared-memory rows, bit 18 of `stages`) pad less than 64-channel ones
+    (2, 73, 73, 80, 192, 3, 3, 1, 0, 0, True, False, 0, 0),         # InceptionV3 conv2d_4: 80 -> 96 instead of 128
+    (3, 35, 35, 96, 96, 3, 3, 1, 1, 1, True, False, 0, 160),        # mixed0..2 3x3: 96 instead of 128, concat-slice store
+    (3, 17, 17, 160, 160, 1, 7, 1, 0, 3, True, False, 0, 0),        # mixed5/6 1x7: 160 instead of 192
+    (5, 17, 17, 160, 192, 7, 1, 1, 3, 0, True, False, 32, 0),       # 7x1, input is a channel slice
+    (2, 17, 17, 128, 128, 1, 7, 1, 0, 3, True, False, 0, 0),        # no padding either way: still the same bits
+]
+
+
+@pytest.mark.parametrize("impl", [7, 8], ids=["one_cta", "cta_pair"])
+@pytest.mark.parametrize("shape", NARROW_ROW_CASES, ids=lambda s: "x".join(map(str, s[:10])))
+def test_conv_tcgen05_halo_kernels_with_64_byte_rows(shape, impl):
+    import torch
+    rng = np.random.default_rng(hash(shape) % 2**32)
+    case = _conv_case(rng, *shape)
+    try:
+        out = _run_conv(impl, case, 0, 1 << 18)
+    except pkg("_lib").DmlError as e:
+        if "does not fit" in str(e):
+            pytest.skip("the whole filter of this layer does not fit next to two halo stages in one CTA's shared memory")
+        raise
+    cout = shape[4]
+    ref = case["ref"]
+    assert (out[..., :cout].float() - ref).abs().max().item() <= 2e-2 * max(1.0, ref.abs().max().item())
+    if shape[13]:
+        assert (out[..., cout:].float() == 7.0).all()
+    assert torch.equal(out, _run_conv(2, case))      # same bits as the im2col kernel
+    try:
+        assert torch.equal(out, _run_conv(impl, case))   # and as the same kernel with 128-byte rows
+    except pkg("_lib").DmlError as e:
+        assert "does not fit" in str(e)  # (with 128-byte rows this layer's filter needs more shared memory than one CTA has)
+
+
 def test_conv_tcgen05_variants_are_bit_identical():
     """Tile shape and kernel variant must not change a single bit (the engine may pick any of them)."""
     import torch
