@@ -2113,8 +2113,10 @@ int tc_init() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_chain_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_duo_kernel) failed: %s", cudaGetErrorString(e));
   e = cudaFuncSetAttribute(conv_tc2x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc2x_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
@@ -2967,11 +2969,14 @@ int launch_chain(const ChainPlan& pl, const ChainArgs& a, cudaStream_t s) {
 
 // ---- conv_duo_kernel: plan + launch over explicit pointers ----
 bool duo_supported(const DuoArgs& a) {
-  if (a.M <= 0 || !a.y2 || !a.we || !a.be || !a.res || !a.out || !a.wr || !a.br || !a.y1n) return false;
+  if (a.M <= 0 || !a.y2 || !a.we || !a.be || !a.out || !a.wr || !a.br || !a.y1n) return false;
+  if ((a.res != nullptr) == (a.src2 != nullptr)) return false;  // exactly one of: identity residual, second GEMM source
   if (a.kmid % 64 || a.kmid < 64 || a.kmid > 256) return false;
+  if (a.k1 % 64 || a.k1 < 64 || a.k1 > a.kmid || (a.src2 ? a.k1 == a.kmid : a.k1 != a.kmid)) return false;
+  if (a.src2 && a.src2_pitch % 8) return false;
   if (a.nexp % 256 || a.nexp < 256 || a.nexp > 2048) return false;
   if (a.nred % 64 || a.nred < 64 || a.nred > 256) return false;
-  if (a.y2_pitch % 8 || a.out_pitch % 8 || a.res_pitch % 8 || a.y1n_pitch % 16) return false;
+  if (a.y2_pitch % 8 || a.out_pitch % 8 || (a.res && a.res_pitch % 8) || a.y1n_pitch % 16) return false;
   if (reinterpret_cast<uintptr_t>(a.y1n) % 32) return false;  // 32-byte vector stores per pixel
   return true;
 }
@@ -3007,11 +3012,14 @@ int duo_plan(DuoPlan* out, const DuoArgs& a, int m_capacity) {
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   };
   CUresult r;
-  if ((r = map2d(&pl.map_y2, a.y2, a.kmid, m_capacity, a.y2_pitch, BLOCK_M, false)) != CUDA_SUCCESS) return tc_fail("duo: y2 map failed (%d)", (int)r);
+  if ((r = map2d(&pl.map_y2, a.y2, a.k1, m_capacity, a.y2_pitch, BLOCK_M, false)) != CUDA_SUCCESS) return tc_fail("duo: y2 map failed (%d)", (int)r);
+  pl.map_s2 = pl.map_y2;
+  if (a.src2 && (r = map2d(&pl.map_s2, a.src2, a.kmid - a.k1, m_capacity, a.src2_pitch, BLOCK_M, false)) != CUDA_SUCCESS) return tc_fail("duo: second-source map failed (%d)", (int)r);
   if ((r = map2d(&pl.map_we, a.we, a.kmid, a.nexp, a.kmid, 32, true)) != CUDA_SUCCESS) return tc_fail("duo: expand weight map failed (%d)", (int)r);
   if ((r = map2d(&pl.map_wr, a.wr, a.nexp, a.nred, a.nexp, a.nred / 2, true)) != CUDA_SUCCESS) return tc_fail("duo: reduce weight map failed (%d)", (int)r);
-  if ((r = map2d(&pl.map_res, a.res, a.nexp, m_capacity, a.res_pitch, BLOCK_M, false)) != CUDA_SUCCESS) return tc_fail("duo: residual map failed (%d)", (int)r);
   if ((r = map2d(&pl.map_out, a.out, a.nexp, m_capacity, a.out_pitch, 16, false)) != CUDA_SUCCESS) return tc_fail("duo: output map failed (%d)", (int)r);
+  pl.map_res = pl.map_out;
+  if (a.res && (r = map2d(&pl.map_res, a.res, a.nexp, m_capacity, a.res_pitch, BLOCK_M, false)) != CUDA_SUCCESS) return tc_fail("duo: residual map failed (%d)", (int)r);
   pl.valid = true;
   *out = pl;
   return 0;
@@ -3024,7 +3032,7 @@ int launch_duo(const DuoPlan& pl, const DuoArgs& a, cudaStream_t s) {
   k.bias2 = a.be; k.bias3 = a.br;
   k.y1n = reinterpret_cast<__nv_bfloat16*>(a.y1n); k.y1n_pitch = a.y1n_pitch;
   k.M = a.M; k.m_tiles = (a.M + 2 * BLOCK_M - 1) / (2 * BLOCK_M);
-  k.kmb = a.kmid / 64; k.nj = a.nexp / 64; k.nred = a.nred;
+  k.kmb = a.kmid / 64; k.kb1 = a.k1 / 64; k.nj = a.nexp / 64; k.nred = a.nred;
   k.y2_bufs = pl.y2_bufs; k.we_stages = pl.we_stages; k.wr_stages = pl.wr_stages; k.ns = pl.slots;
   k.rev = a.rev;
   static const int pf_env = getenv("DML_DUO_PF") ? atoi(getenv("DML_DUO_PF")) : 8;
@@ -3045,8 +3053,14 @@ int launch_duo(const DuoPlan& pl, const DuoArgs& a, cudaStream_t s) {
       cudaMemcpyToSymbol(g_chain_dbg_ptr, &d_word, sizeof d_word);
     }
   }
-  if (prof) launch_pdl(conv_duo_kernel<true>, dim3(2 * clusters), dim3(DUO_THREADS), pl.smem, s, pl.map_y2, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, k);
-  else launch_pdl(conv_duo_kernel<false>, dim3(2 * clusters), dim3(DUO_THREADS), pl.smem, s, pl.map_y2, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, k);
+  const dim3 grid(2 * clusters), block(DUO_THREADS);
+  if (a.res) {
+    if (prof) launch_pdl(conv_duo_kernel<true, true>, grid, block, pl.smem, s, pl.map_y2, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k);
+    else launch_pdl(conv_duo_kernel<false, true>, grid, block, pl.smem, s, pl.map_y2, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k);
+  } else {
+    if (prof) launch_pdl(conv_duo_kernel<true, false>, grid, block, pl.smem, s, pl.map_y2, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k);
+    else launch_pdl(conv_duo_kernel<false, false>, grid, block, pl.smem, s, pl.map_y2, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k);
+  }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return tc_fail("conv_duo_kernel launch: %s", cudaGetErrorString(e));
   if (prof) {
@@ -3198,12 +3212,13 @@ static void duo_args(const Net& net, uint8_t* wts, int lead, int n, PtrFn ptr, D
   const Tensor& ty2 = net.tensors[oe.in];
   a->y2 = ptr(oe.in); a->y2_pitch = ty2.c_pitch;
   a->we = wts + oe.wpack_off; a->be = reinterpret_cast<const float*>(wts + oe.bias_off);
-  a->res = ptr(oe.res); a->res_pitch = net.tensors[oe.res].c_pitch;
+  if (oe.res >= 0) { a->res = ptr(oe.res); a->res_pitch = net.tensors[oe.res].c_pitch; }
+  if (oe.in2 >= 0) { a->src2 = ptr(oe.in2); a->src2_pitch = net.tensors[oe.in2].c_pitch; }
   a->out = ptr(oe.out); a->out_pitch = net.tensors[oe.out].c_pitch;
   a->wr = wts + orr.wpack_off; a->br = reinterpret_cast<const float*>(wts + orr.bias_off);
   a->y1n = ptr(orr.out); a->y1n_pitch = net.tensors[orr.out].c_pitch;
   a->M = n * ty2.h * ty2.w;
-  a->kmid = oe.cin; a->nexp = oe.cout; a->nred = orr.cout;
+  a->k1 = oe.cin; a->kmid = oe.cin + (oe.in2 >= 0 ? oe.cin2 : 0); a->nexp = oe.cout; a->nred = orr.cout;
 }
 
 int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t off_input, size_t off_tc, uint8_t* wts,
@@ -3391,6 +3406,7 @@ int tc_plan(TcPlan* plan, const Net& net, uint8_t* ws, size_t off_arena, size_t 
       const Op& oe = net.ops[i];
       if (oe.duo_red < 0 || plan->chained[i] || plan->chained[oe.duo_red]) continue;
       if (net.tensors[oe.in].buf < 0 || !plan->ops[i].valid || !plan->ops[oe.duo_red].valid || oe.cin_pad != oe.cin) continue;
+      if (oe.in2 >= 0 && (oe.cin2_pad != oe.cin2 || net.tensors[oe.in2].buf < 0)) continue;
       DuoArgs a;
       duo_args(net, wts, (int)i, micro_batch, tptr, &a);
       DuoPlan dp;

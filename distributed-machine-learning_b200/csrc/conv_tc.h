@@ -71,17 +71,19 @@ int launch_chain(const ChainPlan& plan, const ChainArgs& a, cudaStream_t s);
 struct DuoArgs {
   const void* y2 = nullptr; int y2_pitch = 0;      // input of the expand: [M][kmid] bf16 (pitch in elements)
   const void* we = nullptr; const float* be = nullptr;   // packed [nexp][kmid], folded bias
-  const void* res = nullptr; int res_pitch = 0;    // residual [M][nexp]
+  const void* res = nullptr; int res_pitch = 0;    // residual [M][nexp], or nullptr (then src2 is given)
+  const void* src2 = nullptr; int src2_pitch = 0;  // second GEMM source [M][kmid - k1]: the folded projection shortcut's input, or nullptr
   void* out = nullptr; int out_pitch = 0;          // block output [M][nexp]
   const void* wr = nullptr; const float* br = nullptr;   // next block's reduce: packed [nred][nexp], folded bias
   void* y1n = nullptr; int y1n_pitch = 0;          // its output [M][nred]
   int M = 0;                                       // pixels (n * h * w)
-  int kmid = 0, nexp = 0, nred = 0;
+  int kmid = 0, nexp = 0, nred = 0;                // kmid: K of the expand, the second source's channels included
+  int k1 = 0;                                      // channels that come from y2 (= kmid without a second source)
   int rev = 0;  // ConvParams::rev
 };
 struct DuoPlan {
   bool valid = false;
-  alignas(64) CUtensorMap map_y2, map_we, map_wr, map_res, map_out;
+  alignas(64) CUtensorMap map_y2, map_we, map_wr, map_res, map_out, map_s2;
   int y2_bufs = 1, we_stages = 2, wr_stages = 2, slots = 4;
   size_t smem = 0;
   int m_capacity = 0;

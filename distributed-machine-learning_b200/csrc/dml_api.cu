@@ -742,6 +742,7 @@ int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* 
       }
       if (e->use_tc && (size_t)i < e->tc.duos.size() && e->tc.duos[i].valid) {
         // fused duo: this launch also does the next block's reduce; the re-read of `out` never reaches HBM
+        // (a folded projection shortcut's MACs and bytes are in the expand's own figures above)
         const dml::Op& orr = net.ops[op.duo_red];
         const int64_t px = (int64_t)to.h * to.w;
         macs += px * orr.cout * orr.cin;
@@ -852,17 +853,18 @@ int dml_chain_bf16(const void* d_y1, const void* d_w3, const float* d_b3, const 
   return 0;
 }
 
-int dml_duo_bf16(const void* d_y2, const void* d_we, const float* d_be, const void* d_res, void* d_out, const void* d_wr,
-                 const float* d_br, void* d_y1n, int m, int kmid, int nexp, int nred, void* stream) {
+int dml_duo_bf16(const void* d_y2, const void* d_we, const float* d_be, const void* d_res, const void* d_src2, void* d_out,
+                 const void* d_wr, const float* d_br, void* d_y1n, int m, int kmid, int k2, int nexp, int nred, void* stream) {
   if (m < 1) return fail(DML_EINVAL, "m must be positive");
   if (dml::tc_init() != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
   dml::DuoArgs a;
   a.y2 = d_y2; a.y2_pitch = kmid;
   a.we = d_we; a.be = d_be;
   a.res = d_res; a.res_pitch = nexp;
+  a.src2 = d_src2; a.src2_pitch = k2;
   a.out = d_out; a.out_pitch = nexp;
   a.wr = d_wr; a.br = d_br; a.y1n = d_y1n; a.y1n_pitch = nred;
-  a.M = m; a.kmid = kmid; a.nexp = nexp; a.nred = nred;
+  a.M = m; a.k1 = kmid; a.kmid = kmid + (d_src2 ? k2 : 0); a.nexp = nexp; a.nred = nred;
   dml::DuoPlan plan;
   if (dml::duo_plan(&plan, a, m) != 0) return fail(DML_EINVAL, "%s", dml::tc_last_error());
   if (dml::launch_duo(plan, a, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());

@@ -326,8 +326,12 @@ void build_resnet50(Builder& b) {
     for (int oi = 0; oi + 1 < (int)net->ops.size(); ++oi) {
       Op& oe = net->ops[oi];
       Op& orr = net->ops[oi + 1];
-      if (oe.kind != OP_CONV || oe.kh != 1 || oe.kw != 1 || oe.stride != 1 || oe.res < 0 || oe.in2 >= 0 || !oe.relu) continue;
-      if (oe.chain_lead >= 0 || (oe.cin != 128 && oe.cin != 256) || oe.cout != 4 * oe.cin) continue;
+      if (oe.kind != OP_CONV || oe.kh != 1 || oe.kw != 1 || oe.stride != 1 || !oe.relu || oe.cout != 4 * oe.cin) continue;
+      if ((oe.res >= 0) == (oe.in2 >= 0)) continue;
+      // with an identity residual: conv3 / conv4 (conv2's identity blocks run as chains); with the folded projection shortcut as a
+      // second GEMM source on the same pixel grid: conv2_block1 (where the chain kernel loses against the separate layers)
+      if (oe.res >= 0 && (oe.chain_lead >= 0 || (oe.cin != 128 && oe.cin != 256))) continue;
+      if (oe.in2 >= 0 && (oe.stride2 != 1 || oe.cin2 % 64 || oe.cin % 64 || oe.cin + oe.cin2 > 256)) continue;
       if (orr.kind != OP_CONV || orr.kh != 1 || orr.kw != 1 || orr.stride != 1 || orr.in != oe.out || orr.cin != oe.cout ||
           orr.cout != oe.cin || !orr.relu || orr.res >= 0 || orr.in2 >= 0)
         continue;
@@ -335,7 +339,7 @@ void build_resnet50(Builder& b) {
       orr.duo_lead = oi;
       for (int k = oi; k <= oi + 1; ++k) {  // one launch reads and writes all of these
         const Op& m = net->ops[k];
-        for (int t : {m.in, m.out, m.res})
+        for (int t : {m.in, m.out, m.res, m.in2})
           if (t >= 0) { b.touch(t, oi); b.touch(t, oi + 1); }
       }
     }
