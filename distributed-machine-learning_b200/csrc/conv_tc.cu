@@ -2109,9 +2109,12 @@ int tc_init() {
   DML_V6_SHAPES_INIT(DML_V6_ATTR)
 #undef DML_V6_ATTR
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_tc6_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
-  e = cudaFuncSetAttribute(conv_chain_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  e = cudaFuncSetAttribute(conv_chain_kernel<true, false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<false, true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<true, false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<true, false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<false, true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<true, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_chain_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
@@ -2905,7 +2908,6 @@ int launch_chain(const ChainPlan& pl, const ChainArgs& a, cudaStream_t s) {
   k.ahead = ahead_env == 1 ? 1 : 2;
   k.rev = a.rev;
   static const bool prof = getenv("DML_CHAIN_PROF") != nullptr;
-  k.prof = prof ? 1 : 0;
   if (prof) {
     static long long zero[160 * 40] = {};
     cudaMemcpyToSymbol(g_chain_prof, zero, sizeof zero);
@@ -2923,12 +2925,15 @@ int launch_chain(const ChainPlan& pl, const ChainArgs& a, cudaStream_t s) {
       cudaMemcpyToSymbol(g_chain_dbg_ptr, &d_word, sizeof d_word);
     }
   }
-  if (pl.variant == 0)
-    launch_pdl(conv_chain_kernel<true, false, true>, grid, block, pl.smem, s, pl.map_halo, pl.map_w3, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k);
-  else if (pl.variant == 1)
-    launch_pdl(conv_chain_kernel<false, true, true>, grid, block, pl.smem, s, pl.map_halo, pl.map_w3, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k);
-  else
-    launch_pdl(conv_chain_kernel<true, false, false>, grid, block, pl.smem, s, pl.map_halo, pl.map_w3, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k);
+#define DML_CHAIN_LAUNCH(R_, S_, N_)                                                                                                           \
+  do {                                                                                                                                         \
+    if (prof) launch_pdl(conv_chain_kernel<R_, S_, N_, true>, grid, block, pl.smem, s, pl.map_halo, pl.map_w3, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k); \
+    else launch_pdl(conv_chain_kernel<R_, S_, N_, false>, grid, block, pl.smem, s, pl.map_halo, pl.map_w3, pl.map_we, pl.map_wr, pl.map_res, pl.map_out, pl.map_s2, k); \
+  } while (0)
+  if (pl.variant == 0) DML_CHAIN_LAUNCH(true, false, true);
+  else if (pl.variant == 1) DML_CHAIN_LAUNCH(false, true, true);
+  else DML_CHAIN_LAUNCH(true, false, false);
+#undef DML_CHAIN_LAUNCH
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return tc_fail("conv_chain_kernel launch: %s", cudaGetErrorString(e));
   if (prof) {
