@@ -644,7 +644,7 @@ void launch_gap(const void* in, float* out, int n, int hw, int c, int in_pitch, 
 // accumulate).  A 256 x 2048 x 1000 product is too small for a tcgen05 pipeline to pay off and the fp32 CUDA-core
 // kernel above re-reads W once per 8 images; here a CTA owns 32 images x 64 classes and streams K in chunks of 32
 // through a cp.async double buffer.  The fp32 check mode keeps the exact fp32 kernel.
-constexpr int FT_BM = 32, FT_BN = 64, FT_BK = 32, FT_APAD = 36, FT_BPAD = 72, FT_STAGES = 5;
+constexpr int FT_BM = 32, FT_BN = 64, FT_BK = 32, FT_APAD = 36, FT_BPAD = 72, FT_STAGES = 4;  // 4 stages = 55 KB: four CTAs per SM, so the 512 CTAs of a 256-image batch are one wave
 constexpr size_t FT_SMEM = (size_t)FT_STAGES * (FT_BM * FT_APAD + FT_BK * FT_BPAD) * sizeof(float);
 __device__ __forceinline__ uint32_t to_tf32(float v) {
   uint32_t r;
@@ -656,10 +656,15 @@ __device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc, b
   const int bytes = pred ? 16 : 0;  // 0 source bytes: the 16 destination bytes are zero filled
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(bytes) : "memory");
 }
+// Split K: the gridDim.z CTAs of a thread-block cluster (1 x 1 x S) each take cin / S of the K axis; the partial 32 x 64 tiles meet in the
+// shared memory of the cluster's first CTA, which adds them in rank order (deterministic), adds the bias and writes the logits.
+// 128 CTAs walking 64 K chunks one after the other were bound by the latency of each chunk; 512 CTAs walk 16.
 __global__ void __launch_bounds__(128) fc_tf32_kernel(const float* __restrict__ pooled, const float* __restrict__ w,
                                                       const float* __restrict__ b, float* __restrict__ logits, int n, int cin) {
   pdl_launch_dependents();
   pdl_wait();
+  const int ksplit = (int)gridDim.z, krank = (int)blockIdx.z;
+  const int kspan = cin / ksplit, kbase = krank * kspan;
   extern __shared__ __align__(16) float ft_smem[];
   float (*As)[FT_BM][FT_APAD] = reinterpret_cast<float (*)[FT_BM][FT_APAD]>(ft_smem);
   float (*Bs)[FT_BK][FT_BPAD] = reinterpret_cast<float (*)[FT_BK][FT_BPAD]>(ft_smem + FT_STAGES * FT_BM * FT_APAD);
@@ -678,18 +683,18 @@ __global__ void __launch_bounds__(128) fc_tf32_kernel(const float* __restrict__ 
     for (int i = 0; i < 2; ++i) {  // A: 32 rows x 8 float4
       const int idx = tid + i * 128, r = idx >> 3, c4 = (idx & 7) * 4;
       const bool ok = m0 + r < n;
-      cp_async16(&As[st][r][c4], pooled + (int64_t)(ok ? m0 + r : 0) * cin + k0 + c4, ok);
+      cp_async16(&As[st][r][c4], pooled + (int64_t)(ok ? m0 + r : 0) * cin + kbase + k0 + c4, ok);
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {  // B: 32 k rows x 16 float4
       const int idx = tid + i * 128, r = idx >> 4, c4 = (idx & 15) * 4;
       const bool ok = n0 + c4 < 1000;
-      cp_async16(&Bs[st][r][c4], w + (int64_t)(k0 + r) * 1000 + (ok ? n0 + c4 : 0), ok);
+      cp_async16(&Bs[st][r][c4], w + (int64_t)(kbase + k0 + r) * 1000 + (ok ? n0 + c4 : 0), ok);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
 
-  const int nk = cin / FT_BK;
+  const int nk = kspan / FT_BK;
   // FT_STAGES - 1 chunks in flight (L2 latency, not bandwidth, bounds a CTA that waits for every chunk)
   for (int i = 0; i < FT_STAGES - 1; ++i) {
     if (i < nk) load_stage(i, i * FT_BK);
@@ -714,6 +719,38 @@ __global__ void __launch_bounds__(128) fc_tf32_kernel(const float* __restrict__ 
       }
     }
   }
+  if (ksplit > 1) {
+    // every CTA parks its partial tile [32][64] in its own shared memory (the pipeline buffers are done with), the cluster meets,
+    // rank 0 reads the others' tiles through distributed shared memory and adds them in rank order
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    float* part = ft_smem;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = wn + j * 8 + 2 * t;
+      *reinterpret_cast<float2*>(part + (wm + g) * FT_BN + c) = make_float2(acc[j][0], acc[j][1]);
+      *reinterpret_cast<float2*>(part + (wm + g + 8) * FT_BN + c) = make_float2(acc[j][2], acc[j][3]);
+    }
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (krank == 0) {
+      const uint32_t local = (uint32_t)__cvta_generic_to_shared(part);
+      for (int r = 1; r < ksplit; ++r) {
+        uint32_t remote;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(r));
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int c = wn + j * 8 + 2 * t;
+          float2 v0, v1;
+          asm volatile("ld.shared::cluster.v2.f32 {%0, %1}, [%2];" : "=f"(v0.x), "=f"(v0.y) : "r"(remote + (uint32_t)((wm + g) * FT_BN + c) * 4u));
+          asm volatile("ld.shared::cluster.v2.f32 {%0, %1}, [%2];" : "=f"(v1.x), "=f"(v1.y) : "r"(remote + (uint32_t)((wm + g + 8) * FT_BN + c) * 4u));
+          acc[j][0] += v0.x; acc[j][1] += v0.y; acc[j][2] += v1.x; acc[j][3] += v1.y;
+        }
+      }
+    }
+    // nobody leaves while rank 0 may still be reading its shared memory
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (krank != 0) return;
+  }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int col = n0 + wn + j * 8 + 2 * t;
@@ -737,8 +774,21 @@ void init_kernels() {
 
 void launch_fc(const float* pooled, const float* w, const float* b, float* logits, int n, int cin, bool tf32, cudaStream_t s) {
   if (tf32 && cin % FT_BK == 0 && n > 0) {
-    dim3 grid((unsigned)((n + FT_BM - 1) / FT_BM), (1000 + FT_BN - 1) / FT_BN);
-    launch_pdl(fc_tf32_kernel, grid, dim3(128), FT_SMEM, s, pooled, w, b, logits, n, cin);
+    // K split over a cluster of 4 (2) CTAs when cin allows whole 32-element chunks per CTA
+    const unsigned ks = cin % (4 * FT_BK) == 0 ? 4u : (cin % (2 * FT_BK) == 0 ? 2u : 1u);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((n + FT_BM - 1) / FT_BM), (1000 + FT_BN - 1) / FT_BN, ks);
+    cfg.blockDim = dim3(128);
+    cfg.dynamicSmemBytes = FT_SMEM;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = ks;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    cudaLaunchKernelEx(&cfg, fc_tf32_kernel, pooled, w, b, logits, n, cin);
     return;
   }
   dim3 grid((unsigned)((n + FC_IMGS - 1) / FC_IMGS), (1000 + FC_COLS - 1) / FC_COLS);
