@@ -98,7 +98,7 @@ _SIGS = {
     "dml_profile_forward": [_vp, _i, _vp, _vp, _vp, _i, _vp],
     "dml_conv2d_bf16": [_i, _vp, _vp, _vp, _vp, _vp] + [_i] * 17 + [_vp],
     "dml_chain_bf16": [_vp] * 11 + [_i, _i, _i, _vp],
-    "dml_duo_bf16": [_vp] * 9 + [_i, _i, _i, _i, _i, _vp],
+    "dml_duo_bf16": [_vp] * 9 + [_i] * 8 + [_vp],
     "dml_head_static": [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp],
     "dml_sync": [_vp],
 }

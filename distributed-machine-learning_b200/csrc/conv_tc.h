@@ -73,6 +73,8 @@ struct DuoArgs {
   const void* we = nullptr; const float* be = nullptr;   // packed [nexp][kmid], folded bias
   const void* res = nullptr; int res_pitch = 0;    // residual [M][nexp], or nullptr (then src2 is given)
   const void* src2 = nullptr; int src2_pitch = 0;  // second GEMM source [M][kmid - k1]: the folded projection shortcut's input, or nullptr
+  int s2_stride = 1;                               // ... read at this stride from an [n][h * stride][w * stride][kmid - k1] tensor (then n, h, w below are needed)
+  int n = 0, h = 0, w = 0;                         // the output grid, M = n * h * w (only for s2_stride > 1)
   void* out = nullptr; int out_pitch = 0;          // block output [M][nexp]
   const void* wr = nullptr; const float* br = nullptr;   // next block's reduce: packed [nred][nexp], folded bias
   void* y1n = nullptr; int y1n_pitch = 0;          // its output [M][nred]
@@ -85,6 +87,7 @@ struct DuoPlan {
   bool valid = false;
   alignas(64) CUtensorMap map_y2, map_we, map_wr, map_res, map_out, map_s2;
   int y2_bufs = 1, we_stages = 2, wr_stages = 2, slots = 4;
+  bool no_slack = false;  // the shared-memory request leaves no room to align the base (it is 1 KiB-aligned in practice; the kernel checks)
   size_t smem = 0;
   int m_capacity = 0;
   float ms = 0.f, ms_separate = 0.f;  // autotune: this kernel against the two separate ones

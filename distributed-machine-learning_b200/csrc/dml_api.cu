@@ -854,14 +854,17 @@ int dml_chain_bf16(const void* d_y1, const void* d_w3, const float* d_b3, const 
 }
 
 int dml_duo_bf16(const void* d_y2, const void* d_we, const float* d_be, const void* d_res, const void* d_src2, void* d_out,
-                 const void* d_wr, const float* d_br, void* d_y1n, int m, int kmid, int k2, int nexp, int nred, void* stream) {
-  if (m < 1) return fail(DML_EINVAL, "m must be positive");
+                 const void* d_wr, const float* d_br, void* d_y1n, int n, int h, int w, int kmid, int k2, int s2_stride, int nexp,
+                 int nred, void* stream) {
+  const int m = n * h * w;
+  if (n < 1 || h < 1 || w < 1) return fail(DML_EINVAL, "n, h, w must be positive");
   if (dml::tc_init() != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
   dml::DuoArgs a;
   a.y2 = d_y2; a.y2_pitch = kmid;
   a.we = d_we; a.be = d_be;
   a.res = d_res; a.res_pitch = nexp;
-  a.src2 = d_src2; a.src2_pitch = k2;
+  a.src2 = d_src2; a.src2_pitch = k2; a.s2_stride = d_src2 ? s2_stride : 1;
+  a.n = n; a.h = h; a.w = w;
   a.out = d_out; a.out_pitch = nexp;
   a.wr = d_wr; a.br = d_br; a.y1n = d_y1n; a.y1n_pitch = nred;
   a.M = m; a.k1 = kmid; a.kmid = kmid + (d_src2 ? k2 : 0); a.nexp = nexp; a.nred = nred;

@@ -331,7 +331,9 @@ void build_resnet50(Builder& b) {
       // with an identity residual: conv3 / conv4 (conv2's identity blocks run as chains); with the folded projection shortcut as a
       // second GEMM source on the same pixel grid: conv2_block1 (where the chain kernel loses against the separate layers)
       if (oe.res >= 0 && (oe.chain_lead >= 0 || (oe.cin != 128 && oe.cin != 256))) continue;
-      if (oe.in2 >= 0 && (oe.stride2 != 1 || oe.cin2 % 64 || oe.cin % 64 || oe.cin + oe.cin2 > 256)) continue;
+      // (at stride 2 -- conv3_block1, K = 128 + 256 -- the kernel reads the shortcut's input through an im2col-mode tensor map; conv4 / conv5's
+      // first blocks have K = 768 / 1536: their 128-pixel tile of A alone is 192 / 384 KB)
+      if (oe.in2 >= 0 && (oe.stride2 > 2 || oe.cin2 % 64 || oe.cin % 64 || oe.cin + oe.cin2 > 384)) continue;
       if (orr.kind != OP_CONV || orr.kh != 1 || orr.kw != 1 || orr.stride != 1 || orr.in != oe.out || orr.cin != oe.cout ||
           orr.cout != oe.cin || !orr.relu || orr.res >= 0 || orr.in2 >= 0)
         continue;

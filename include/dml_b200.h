@@ -212,14 +212,15 @@ int dml_chain_bf16(const void* d_y1, const void* d_w3, const float* d_b3, const 
 
 /* A ResNet50 block's 1x1 expand with its shortcut and the NEXT block's 1x1 reduce of predict (models.py:65; Keras block1:
  * _3_conv -> Add -> ReLU, then _1_conv) as ONE kernel over explicit device buffers, all bf16 with contiguous channels:
- * y2 [m][kmid] -> out [m][nexp] = relu(We y2 (+ Wp src2) + be (+ res)) -> y1n [m][nred] = relu(Wr out + br); m = n * h * w
- * pixels (any m: partial tiles are clipped).  Exactly one of d_res ([m][nexp], the identity shortcut: conv3 / conv4) and d_src2
- * ([m][k2], the projection shortcut's input folded in as a second GEMM source: conv2_block1; We then holds [nexp][kmid + k2])
- * is given.  kmid, k2 multiples of 64 with kmid + k2 <= 256, nexp a multiple of 256, nred in {64, 128, 192, 256}.  Weights
- * packed as for dml_conv2d_bf16.  Results are bit-identical to the two dml_conv2d_bf16 calls it replaces.  The unit-test hook
- * of that kernel. */
+ * y2 [n][h][w][kmid] -> out [n][h][w][nexp] = relu(We y2 (+ Wp src2) + be (+ res)) -> y1n [n][h][w][nred] = relu(Wr out + br)
+ * (any n * h * w: partial tiles are clipped).  Exactly one of d_res ([n][h][w][nexp], the identity shortcut: conv3 / conv4) and
+ * d_src2 (the projection shortcut's input folded in as a second GEMM source, [n][h * s2_stride][w * s2_stride][k2] read at stride
+ * s2_stride = 1 (conv2_block1) or 2 (conv3_block1); We then holds [nexp][kmid + k2]) is given.  kmid, k2 multiples of 64 with
+ * kmid + k2 <= 384, nexp a multiple of 256, nred in {64, 128, 192, 256}.  Weights packed as for dml_conv2d_bf16.  Results are
+ * bit-identical to the two dml_conv2d_bf16 calls it replaces.  The unit-test hook of that kernel. */
 int dml_duo_bf16(const void* d_y2, const void* d_we, const float* d_be, const void* d_res, const void* d_src2, void* d_out,
-                 const void* d_wr, const float* d_br, void* d_y1n, int m, int kmid, int k2, int nexp, int nred, void* stream);
+                 const void* d_wr, const float* d_br, void* d_y1n, int n, int h, int w, int kmid, int k2, int s2_stride, int nexp,
+                 int nred, void* stream);
 
 /* The dense(1000) + softmax + top-5 head with NO device allocation anywhere: no
  * engine, no workspace.  (No counterpart in the reference: its Keras model owns

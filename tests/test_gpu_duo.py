@@ -13,7 +13,7 @@ from conftest import pkg
 pytestmark = pytest.mark.gpu
 
 
-def _case(n, h, w, kmid, seed, k2=0):
+def _case(n, h, w, kmid, seed, k2=0, s2=1):
     import torch
     rng = np.random.default_rng(seed)
     dev = torch.device("cuda")
@@ -22,12 +22,12 @@ def _case(n, h, w, kmid, seed, k2=0):
     def t(shape, scale=1.0, dtype=torch.bfloat16):
         return torch.from_numpy((rng.standard_normal(shape) * scale).astype(np.float32)).to(dev).to(dtype)
 
-    c = dict(n=n, h=h, w=w, kmid=kmid, nexp=nexp, nred=nred, k2=k2)
+    c = dict(n=n, h=h, w=w, kmid=kmid, nexp=nexp, nred=nred, k2=k2, s2=s2)
     c["y2"] = t((n, h, w, kmid)).relu()
     c["we"] = t((nexp, kmid + k2), 1 / np.sqrt(kmid + k2))
     c["be"] = t((nexp,), 0.1, torch.float32)
     c["res"] = t((n, h, w, nexp)).relu() if k2 == 0 else None      # identity shortcut ...
-    c["src2"] = t((n, h, w, k2)).relu() if k2 else None              # ... or the projection shortcut's input as a second GEMM source
+    c["src2"] = t((n, h * s2, w * s2, k2)).relu() if k2 else None    # ... or the projection shortcut's input (read at stride s2) as a second GEMM source
     c["wr"] = t((nred, nexp), 1 / np.sqrt(nexp))
     c["br"] = t((nred,), 0.1, torch.float32)
     return c
@@ -44,7 +44,7 @@ def _fused(c):
     out = torch.full((n, h, w, c["nexp"]), 7.0, dtype=torch.bfloat16, device="cuda")
     y1n = torch.full((n, h, w, c["nred"]), 7.0, dtype=torch.bfloat16, device="cuda")
     lib.check(lib.lib().dml_duo_bf16(c["y2"].data_ptr(), c["we"].data_ptr(), c["be"].data_ptr(), _ptr(c["res"]), _ptr(c["src2"]), out.data_ptr(),
-                                     c["wr"].data_ptr(), c["br"].data_ptr(), y1n.data_ptr(), n * h * w, c["kmid"], c["k2"], c["nexp"], c["nred"], None))
+                                     c["wr"].data_ptr(), c["br"].data_ptr(), y1n.data_ptr(), n, h, w, c["kmid"], c["k2"], c["s2"], c["nexp"], c["nred"], None))
     torch.cuda.synchronize()
     return out, y1n
 
@@ -65,7 +65,7 @@ def _separate(c):
     n, h, w = c["n"], c["h"], c["w"]
     if c["src2"] is not None:
         # the folded projection shortcut = more K blocks: the same GEMM over the concatenated channels
-        x = torch.cat([c["y2"], c["src2"]], dim=-1).contiguous()
+        x = torch.cat([c["y2"], c["src2"][:, ::c["s2"], ::c["s2"], :]], dim=-1).contiguous()
         out = _conv(x, c["we"], c["be"], None, n, h, w, c["kmid"] + c["k2"], c["nexp"])
     else:
         out = _conv(c["y2"], c["we"], c["be"], c["res"], n, h, w, c["kmid"], c["nexp"])
@@ -80,7 +80,7 @@ def torch_cat(a, b):
 
 def _torch_reference(c):
     if c["src2"] is not None:
-        o = torch_cat(c["y2"], c["src2"]).float() @ c["we"].float().t() + c["be"]
+        o = torch_cat(c["y2"], c["src2"][:, ::c["s2"], ::c["s2"], :]).float() @ c["we"].float().t() + c["be"]
     else:
         o = c["y2"].float() @ c["we"].float().t() + c["be"] + c["res"].float()
     out = o.relu().bfloat16().float()
@@ -88,12 +88,13 @@ def _torch_reference(c):
     return out, y1n
 
 
-@pytest.mark.parametrize("n,h,w,kmid,k2", [(1, 14, 14, 256, 0), (3, 28, 28, 128, 0), (40, 28, 28, 128, 0), (37, 14, 14, 256, 0),
-                                           (256, 14, 14, 256, 0), (70, 28, 28, 128, 0), (2, 16, 16, 64, 0), (5, 12, 12, 192, 0),
-                                           (1, 56, 56, 64, 64), (37, 56, 56, 64, 64), (3, 20, 20, 128, 64)])
-def test_duo_matches_separate_kernels_bit_for_bit(n, h, w, kmid, k2):
+@pytest.mark.parametrize("n,h,w,kmid,k2,s2", [(1, 14, 14, 256, 0, 1), (3, 28, 28, 128, 0, 1), (40, 28, 28, 128, 0, 1), (37, 14, 14, 256, 0, 1),
+                                              (256, 14, 14, 256, 0, 1), (70, 28, 28, 128, 0, 1), (2, 16, 16, 64, 0, 1), (5, 12, 12, 192, 0, 1),
+                                              (1, 56, 56, 64, 64, 1), (37, 56, 56, 64, 64, 1), (3, 20, 20, 128, 64, 1),
+                                              (1, 28, 28, 128, 256, 2), (37, 28, 28, 128, 256, 2), (5, 10, 10, 64, 128, 2)])
+def test_duo_matches_separate_kernels_bit_for_bit(n, h, w, kmid, k2, s2):
     import torch
-    c = _case(n, h, w, kmid, seed=n + kmid, k2=k2)
+    c = _case(n, h, w, kmid, seed=n + kmid, k2=k2, s2=s2)
     out, y1n = _fused(c)
     out_s, y1n_s = _separate(c)
     assert torch.equal(out, out_s)
@@ -110,7 +111,7 @@ def test_duo_refuses_what_it_cannot_tile():
     out = torch.empty((64, 512), dtype=torch.bfloat16, device="cuda")
     y = torch.empty((64, 128), dtype=torch.bfloat16, device="cuda")
     rc = lib.lib().dml_duo_bf16(c["y2"].data_ptr(), c["we"].data_ptr(), c["be"].data_ptr(), c["res"].data_ptr(), None, out.data_ptr(),
-                                c["wr"].data_ptr(), c["br"].data_ptr(), y.data_ptr(), 64, 96, 0, 512, 128, None)  # kmid not a multiple of 64
+                                c["wr"].data_ptr(), c["br"].data_ptr(), y.data_ptr(), 1, 8, 8, 96, 0, 1, 512, 128, None)  # kmid not a multiple of 64
     assert rc == -1 and b"not eligible" in lib.lib().dml_last_error()
 
 
@@ -128,7 +129,7 @@ def test_engine_with_and_without_the_duo_gives_the_same_bits(images, monkeypatch
         eng = pkg("engine").Engine("ResNet50", max_batch=40, weights=W)
         try:
             names = [o[0] for o in eng.ops() if o[1] == 0 and o[3] == 0]  # convs that report no work of their own: duo members
-            assert (len(names) == 7) == duo, names  # next-block reduces: conv2_block2's (behind the folded shortcut), 2 in conv3, 4 in conv4
+            assert (len(names) == 8) == duo, names  # next-block reduces: conv2_block2's and conv3_block2's (behind folded shortcuts), 2 more in conv3, 4 in conv4
             idx, prob, probs = eng.predict_images(sel, want_probs=True)
             outs.append((idx, prob, probs, eng.logits(len(sel)).cpu().numpy()))
         finally:

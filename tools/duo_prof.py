@@ -34,7 +34,7 @@ def main():
 
     def fused():
         lib.check(lib.lib().dml_duo_bf16(y2.data_ptr(), we.data_ptr(), be.data_ptr(), res.data_ptr(), None, out.data_ptr(), wr.data_ptr(),
-                                         br.data_ptr(), y1n.data_ptr(), m, kmid, 0, nexp, nred, None))
+                                         br.data_ptr(), y1n.data_ptr(), n, h, w, kmid, 0, 1, nexp, nred, None))
 
     def conv(x, wp, b, r, o, cin, cout):
         lib.check(lib.lib().dml_conv2d_bf16(5, x.data_ptr(), wp.data_ptr(), b.data_ptr(), r.data_ptr() if r is not None else None, o.data_ptr(),
