@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "libdml_b200.so")
 SOURCES = ["dml_api.cu", "kernels.cu", "conv_tc.cu", "stem_tc.cu", "head_static.cu", "graph.cc"]
-HEADERS = ["conv_tc.h", "conv_chain.inc", "conv_duo.inc", "graph.h", "kernels.h", os.path.join("..", "..", "include", "dml_b200.h")]
+HEADERS = ["conv_tc.h", "conv_chain.inc", "conv_duo.inc", "conv_pool.inc", "graph.h", "kernels.h", os.path.join("..", "..", "include", "dml_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -99,6 +99,7 @@ _SIGS = {
     "dml_conv2d_bf16": [_i, _vp, _vp, _vp, _vp, _vp] + [_i] * 17 + [_vp],
     "dml_chain_bf16": [_vp] * 11 + [_i, _i, _i, _vp],
     "dml_duo_bf16": [_vp] * 9 + [_i] * 8 + [_vp],
+    "dml_conv_pool_bf16": [_vp] * 4 + [_i] * 10 + [_vp],
     "dml_head_static": [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp],
     "dml_sync": [_vp],
 }

@@ -2025,6 +2025,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc5_kernel(const __grid_co
 
 #include "conv_chain.inc"
 #include "conv_duo.inc"
+#include "conv_pool.inc"
 
 }  // namespace
 
@@ -2116,6 +2117,8 @@ int tc_init() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<false, true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_chain_kernel<true, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) return tc_fail("cudaFuncSetAttribute(conv_chain_kernel, smem %d): %s", SMEM_LIMIT, cudaGetErrorString(e));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6p_kernel<4, 4, 1, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc6p_kernel<3, 3, 1, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_duo_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
@@ -3116,6 +3119,68 @@ int launch_duo(const DuoPlan& pl, const DuoArgs& a, cudaStream_t s) {
       fprintf(stderr, "[duo debug] wait id %llu timed out at index %llu, block %llu, warp %llu (%s)\n", *h_word & 0xff, (*h_word >> 8) & 0xffff,
               (*h_word >> 24) & 0xffff, (*h_word >> 40) & 0xff, cudaGetErrorString(se));
   }
+  return 0;
+}
+
+// ---- conv_tc6p_kernel: plan + launch ----
+int conv_pool_plan(ConvPoolPlan* out, const ConvParams& p, int hp, int wq, int pool_pad, int n_capacity) {
+  if (p.cout != V6P_BN || p.stride != 1 || p.res != nullptr || p.in2 != nullptr || p.norelu_cols != 0)
+    return tc_fail("conv + pool kernel: needs a stride-1 convolution with 64 filters and no residual");
+  if (pool_pad != 0 && pool_pad != 1) return tc_fail("conv + pool kernel: pool padding %d", pool_pad);
+  if (pool_pad && !p.relu) return tc_fail("conv + pool kernel: the pool's zero padding needs the ReLU in front of it");
+  if (hp != (p.ho + 2 * pool_pad - 3) / 2 + 1 || wq != (p.wo + 2 * pool_pad - 3) / 2 + 1) return tc_fail("conv + pool kernel: pooled size %d x %d does not follow from %d x %d", hp, wq, p.ho, p.wo);
+  ConvPoolPlan pl;
+  TcTune tune;
+  tune.version = 6;
+  if (tc_plan_one(&pl.conv, p, n_capacity, tune) != 0) return -1;
+  const TcOpPlan& c = pl.conv;
+  if (c.version != 6 || c.bn != V6P_BN) return tc_fail("conv + pool kernel: the filter does not fit in one CTA's shared memory");
+  const bool shape_ok = (p.kh == 4 && p.kw == 4 && c.cpb == 1 && c.row_bytes == 32) || (p.kh == 3 && p.kw == 3 && c.cpb == 1 && c.row_bytes == 64);
+  if (!shape_ok) return tc_fail("conv + pool kernel: no instance for %dx%d taps, %d channel blocks of %d-byte rows", p.kh, p.kw, c.cpb, c.row_bytes);
+  const int taps = p.kh * p.kw;
+  const size_t b_bytes = ((size_t)taps * c.cpb * V6P_BN * c.row_bytes + 1023) / 1024 * 1024;
+  pl.hp = hp; pl.wq = wq; pl.pool_pad = pool_pad; pl.a_stages = 2;
+  // pooled rows per band: the most useful rows per issued MMA row among the band buffers that fit beside two halo stages
+  double best = 0;
+  for (int R = 1; R <= 16 && R <= hp; ++R) {
+    const size_t band = (size_t)(2 * R + 1) * p.wo * 128;
+    const size_t smem = 1024 + b_bytes + (size_t)pl.a_stages * c.a_stage_bytes + band + V6P_BN * 4 + 16 + 256;
+    if (smem > (size_t)SMEM_LIMIT || (2 * R + 1) * c.wp + BLOCK_M >= 65536) break;
+    const int T = ((2 * R + 1) * c.wp + BLOCK_M - 1) / BLOCK_M;
+    const int bands = (hp + R - 1) / R;
+    const double eff = (double)hp * 2 * p.wo / ((double)bands * T * BLOCK_M);  // new convolution rows per issued MMA row
+    if (eff > best) { best = eff; pl.R = R; pl.T = T; pl.bands = bands; pl.smem = smem; }
+  }
+  if (pl.R == 0) return tc_fail("conv + pool kernel: no band of pooled rows fits in shared memory (row of %d pixels)", p.wo);
+  pl.valid = true;
+  *out = pl;
+  return 0;
+}
+
+int launch_conv_pool(const ConvPoolPlan& pl, const ConvParams& p, void* pool_out, int pool_out_pitch, int pool_out_img0, cudaStream_t s) {
+  if (!pl.valid) return tc_fail("conv + pool plan is not valid");
+  const TcOpPlan& c = pl.conv;
+  if (p.n > c.m_capacity) return tc_fail("batch of %d images exceeds the planned capacity", p.n);
+  if (pool_out_pitch % 8 || reinterpret_cast<uintptr_t>(pool_out) % 16) return tc_fail("conv + pool kernel: the pooled rows must be 16-byte aligned");
+  TcV6pParams k{};
+  k.bias = p.bias;
+  k.out = reinterpret_cast<__nv_bfloat16*>(pool_out);
+  k.n_img = p.n; k.ho = p.ho; k.wo = p.wo; k.wp = c.wp;
+  k.hp = pl.hp; k.wq = pl.wq; k.out_pitch = pool_out_pitch; k.pool_pad = pl.pool_pad;
+  k.pad_h = p.pad_h; k.pad_w = p.in_row_cells ? 0 : p.pad_w;
+  k.R = pl.R; k.bands = pl.bands; k.T = pl.T;
+  k.rows_box = c.rows_box; k.a_cb_bytes = c.a_cb_bytes; k.a_stage_bytes = c.a_stage_bytes; k.a_stages = pl.a_stages;
+  k.relu = p.relu; k.tmem_cols = 4 * V6P_BN;
+  k.in_img0 = p.in_img0; k.out_img0 = pool_out_img0;
+  k.last_kmma = (p.cin - (c.cpb - 1) * (c.row_bytes / 2) + 15) / 16;
+  k.cin_pad = p.cin_pad;
+  k.inv_wp = 1.0f / (float)c.wp;
+  const int units = p.n * pl.bands;
+  const int grid = units < g_num_sms ? units : g_num_sms;
+  if (p.kh == 4) launch_pdl(conv_tc6p_kernel<4, 4, 1, 32>, dim3(grid), dim3(TC6_THREADS), pl.smem, s, c.map_a, c.map_b, k);
+  else launch_pdl(conv_tc6p_kernel<3, 3, 1, 64>, dim3(grid), dim3(TC6_THREADS), pl.smem, s, c.map_a, c.map_b, k);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return tc_fail("conv_tc6p_kernel launch: %s", cudaGetErrorString(e));
   return 0;
 }
 

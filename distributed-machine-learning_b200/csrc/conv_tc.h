@@ -96,6 +96,18 @@ bool duo_supported(const DuoArgs& a);
 int duo_plan(DuoPlan* out, const DuoArgs& a, int m_capacity);
 int launch_duo(const DuoPlan& plan, const DuoArgs& a, cudaStream_t s);
 
+// A stride-1 convolution with 64 filters and the 3x3 stride-2 max-pool behind it as one kernel (conv_pool.inc).
+struct ConvPoolPlan {
+  bool valid = false;
+  TcOpPlan conv;   // the resident-filter halo plan of the convolution (tensor maps, tile geometry)
+  int hp = 0, wq = 0, pool_pad = 0, R = 0, bands = 0, T = 0, a_stages = 2;
+  size_t smem = 0;
+  float ms = 0.f, ms_separate = 0.f;  // autotune: this kernel against convolution + pool
+};
+// p: the convolution (p.out is not written); the pool's output is [n][hp][wq][pool_out_pitch] at launch time.
+int conv_pool_plan(ConvPoolPlan* out, const ConvParams& p, int hp, int wq, int pool_pad, int n_capacity);
+int launch_conv_pool(const ConvPoolPlan& plan, const ConvParams& p, void* pool_out, int pool_out_pitch, int pool_out_img0, cudaStream_t s);
+
 struct TcPlan {
   std::vector<TcOpPlan> ops;  // indexed like Net::ops
   std::vector<DuoPlan> duos;  // indexed like Net::ops; valid at the expand that leads a duo the engine runs fused

@@ -87,6 +87,7 @@ struct dml_engine {
   bool s2d = false;          // K1 writes the space-to-depth input and the stem runs as a stride-1 halo conv (Net::S2d)
   size_t input_img_bytes = 0;
   dml::TcOpPlan stem_plan;
+  std::vector<dml::ConvPoolPlan> conv_pool;  // indexed like Net::ops: valid where the conv and the max-pool behind it run as one kernel
   // Branch streams (graph.h, plan_streams): engine-owned side streams and one event per op another stream waits for.
   bool branch_streams = false;
   cudaStream_t side[7] = {};
@@ -160,6 +161,99 @@ int plan_stem(dml_engine* e) {
   return 0;
 }
 
+// ConvParams of conv op oi over the engine's tensors (the stem in its space-to-depth form), as run_layers builds them.
+dml::ConvParams conv_params_of(const dml_engine* e, int oi, int img0, int cnt) {
+  const dml::Net& net = e->net;
+  if (e->s2d && oi == net.s2d.op) return stem_s2d_params(e, img0, cnt);
+  const dml::Op& op = net.ops[oi];
+  const dml::Tensor& ti = net.tensors[op.in];
+  const dml::Tensor& to = net.tensors[op.out];
+  dml::ConvParams p{};
+  p.in = e->tensor_ptr(op.in, img0);
+  p.w = e->wts + op.merged_w_off;
+  p.bias = reinterpret_cast<const float*>(e->wts + op.merged_b_off);
+  p.out = e->tensor_ptr(op.out, img0);
+  p.n = cnt; p.hi = ti.h; p.wi = ti.w; p.cin = op.cin; p.in_pitch = ti.c_pitch;
+  p.ho = to.h; p.wo = to.w; p.cout = op.cout; p.out_pitch = to.c_pitch;
+  p.kh = op.kh; p.kw = op.kw; p.stride = op.stride; p.pad_h = op.pad_h; p.pad_w = op.pad_w;
+  p.cin_pad = op.cin_pad; p.relu = op.relu;
+  return p;
+}
+
+// Convolution + max-pool pairs that may run as one kernel (conv_pool.inc): a stride-1 conv with 64 filters whose output is read by
+// nothing but a 3x3 stride-2 max-pool (ResNet50 conv1 + pool1, InceptionV3 conv2d_2 + max_pooling2d).  Timed against the two kernels.
+int plan_conv_pools(dml_engine* e) {
+  const dml::Net& net = e->net;
+  e->conv_pool.assign(net.ops.size(), dml::ConvPoolPlan());
+  if (!e->use_tc || e->keep_all || getenv("DML_NO_CONV_POOL")) return 0;
+  const bool tune_log = getenv("DML_TUNE_LOG") != nullptr;
+  for (size_t i = 0; i + 1 < net.ops.size(); ++i) {
+    const dml::Op& op = net.ops[i];
+    const dml::Op& po = net.ops[i + 1];
+    if (op.kind != dml::OP_CONV || op.skip || op.merged_cout > 0 || op.cout != 64 || op.res >= 0 || op.in2 >= 0 || !op.relu) continue;
+    if (po.kind != dml::OP_MAXPOOL || po.in != op.out || po.kh != 3 || po.stride != 2 || po.pad_h > 1) continue;
+    if (i < e->tc.chained.size() && e->tc.chained[i]) continue;
+    const bool stem = e->s2d && (int)i == net.s2d.op;
+    if (!stem && (op.stride != 1 || i >= e->tc.ops.size() || !e->tc.ops[i].valid)) continue;
+    bool other_reader = false;
+    for (size_t j = 0; j < net.ops.size(); ++j)
+      if (j != i + 1 && (net.ops[j].in == op.out || net.ops[j].res == op.out || net.ops[j].in2 == op.out)) other_reader = true;
+    if (other_reader) continue;
+    const dml::Tensor& tp = net.tensors[po.out];
+    dml::ConvParams p = conv_params_of(e, (int)i, 0, e->micro_batch);
+    dml::ConvPoolPlan cp;
+    if (dml::conv_pool_plan(&cp, p, tp.h, tp.w, po.pad_h, e->max_batch) != 0) {
+      if (tune_log) fprintf(stderr, "[tune] conv + pool at %s not planned: %s\n", op.name.c_str(), dml::tc_last_error());
+      continue;
+    }
+    void* pool_out = e->tensor_ptr(po.out, 0);
+    bool use = true;
+    if (!getenv("DML_NO_AUTOTUNE") && !getenv("DML_FORCE_CONV_POOL")) {
+      cudaEvent_t e0, e1;
+      if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) return fail(DML_ECUDA, "cudaEventCreate failed");
+      const dml::Tensor& to = net.tensors[op.out];
+      dml::PoolParams pp{};
+      pp.in = e->tensor_ptr(po.in, 0); pp.out = pool_out;
+      pp.n = e->micro_batch; pp.hi = to.h; pp.wi = to.w; pp.c = to.c; pp.in_pitch = to.c_pitch;
+      pp.ho = tp.h; pp.wo = tp.w; pp.out_pitch = tp.c_pitch; pp.k = 3; pp.stride = 2; pp.pad = po.pad_h;
+      float best[2] = {1e30f, 1e30f};
+      for (int v = 0; v < 2; ++v) {
+        auto run = [&]() -> bool {
+          if (v == 0) {
+            if (dml::launch_conv_tc_plan(stem ? e->stem_plan : e->tc.ops[i], p, nullptr) != 0) return false;
+            dml::launch_maxpool(pp, false, nullptr);
+            return true;
+          }
+          return dml::launch_conv_pool(cp, p, pool_out, tp.c_pitch, 0, nullptr) == 0;
+        };
+        bool ok = run() && cudaDeviceSynchronize() == cudaSuccess;
+        for (int rep = 0; ok && rep < 3; ++rep) {
+          cudaEventRecord(e0, nullptr);
+          for (int k = 0; k < 4; ++k) ok = ok && run();
+          cudaEventRecord(e1, nullptr);
+          ok = ok && cudaEventSynchronize(e1) == cudaSuccess;
+          float ms = 0.f;
+          if (ok) cudaEventElapsedTime(&ms, e0, e1);
+          if (ok && ms / 4.f < best[v]) best[v] = ms / 4.f;
+        }
+        if (!ok) {
+          cudaEventDestroy(e0); cudaEventDestroy(e1);
+          return fail(DML_ECUDA, "conv + pool timing failed at %s: %s / %s", op.name.c_str(), dml::tc_last_error(), cudaGetErrorString(cudaGetLastError()));
+        }
+      }
+      cudaEventDestroy(e0);
+      cudaEventDestroy(e1);
+      cp.ms = best[1]; cp.ms_separate = best[0];
+      use = best[1] < best[0];
+      if (tune_log)
+        fprintf(stderr, "[tune] conv + pool %s + %s (bands of %d pooled rows, %d tiles): fused %.4f ms, separate %.4f ms -> %s\n", op.name.c_str(),
+                po.name.c_str(), cp.R, cp.T, best[1], best[0], use ? "fused" : "separate");
+    }
+    if (use) e->conv_pool[i] = cp;
+  }
+  return 0;
+}
+
 // Streams and events of the branch schedule.  Measured on InceptionV3 batch 128 (B200): 47.2k -> 50.9k images/s.  The kernels
 // keep their full grids: capping the SMs of the convolutions that run side by side (equal caps of 50 / 75 %, or shares in
 // proportion to their measured times) lost 3 - 10 %, stream priorities changed nothing.
@@ -215,6 +309,22 @@ int run_layers(dml_engine* e, int img0, int cnt, cudaStream_t s0) {
         p.hi2 = t2.h; p.wi2 = t2.w; p.cin2 = op.cin2; p.in2_pitch = t2.c_pitch; p.stride2 = op.stride2; p.cin2_pad = op.cin2_pad;
       }
       int nl = 0;
+      if (oi < e->conv_pool.size() && e->conv_pool[oi].valid) {
+        // this convolution and the max-pool behind it as one kernel: the pool op (oi + 1) is done here
+        const dml::Op& po = net.ops[oi + 1];
+        if (multi)
+          for (int w : po.waits) CUDA_TRY(cudaStreamWaitEvent(s, e->op_event[w], 0));
+        dml::ConvParams pc = conv_params_of(e, (int)oi, img0, cnt);
+        if (dml::launch_conv_pool(e->conv_pool[oi], pc, e->tensor_ptr(po.out, img0), net.tensors[po.out].c_pitch, 0, s) != 0)
+          return fail(DML_ECUDA, "conv + pool kernel launch failed at %s: %s", op.name.c_str(), dml::tc_last_error());
+        e->launches += 1;
+        e->prof_end(s);
+        if (multi && po.signal) CUDA_TRY(cudaEventRecord(e->op_event[oi + 1], s));
+        if (multi && op.signal) CUDA_TRY(cudaEventRecord(e->op_event[oi], s));
+        if (pingpong) rev ^= 1;  // (the pool's turn)
+        ++oi;
+        continue;
+      }
       if (e->use_tc && oi < e->tc.chains.size() && e->tc.chains[oi].valid) {
         // 3x3 + expand (+ residual / folded shortcut) + the next block's reduce as one kernel
         if (dml::launch_chain_tc(e->tc, net, e->wts, (int)oi, cnt, e->ws, e->off_arena, s, rev) != 0)
@@ -462,6 +572,7 @@ int dml_bind_workspace(dml_engine* e, void* dev_ptr, size_t bytes) {
       return fail(DML_ECUDA, "tcgen05 plan failed: %s", dml::tc_last_error());
     if (plan_stem(e) != 0) return DML_ECUDA;
     if (int rc = plan_branch_streams(e)) return rc;
+    if (int rc = plan_conv_pools(e)) return rc;
   }
   return 0;
 }
@@ -480,6 +591,7 @@ int dml_bind_weights(dml_engine* e, void* dev_ptr, size_t bytes) {
       return fail(DML_ECUDA, "tcgen05 plan failed: %s", dml::tc_last_error());
     if (plan_stem(e) != 0) return DML_ECUDA;
     if (int rc = plan_branch_streams(e)) return rc;
+    if (int rc = plan_conv_pools(e)) return rc;
   }
   return 0;
 }
@@ -705,7 +817,8 @@ int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* 
     const int cout_x = op.merged_cout > 0 ? op.merged_cout : op.cout;
     nm = op.name; k = (int)op.kind;
     const bool chained = e->use_tc && (size_t)i < e->tc.chained.size() && e->tc.chained[i];
-    if (op.skip || chained) {  // a follower of a merged 1x1 pair / a member of a fused chain: reported by its leader
+    const bool pooled_by_conv = i > 0 && (size_t)(i - 1) < e->conv_pool.size() && e->conv_pool[i - 1].valid;  // done inside the conv's launch
+    if (op.skip || chained || pooled_by_conv) {  // a follower of a merged 1x1 pair / a member of a fused chain: reported by its leader
       if (name && name_cap > 0) snprintf(name, name_cap, "%s", nm.c_str());
       if (kind) *kind = k;
       if (impl) *impl = e->use_tc ? 1 : 0;
@@ -739,6 +852,11 @@ int dml_op_info(dml_engine* e, int i, char* name, int name_cap, int* kind, int* 
           wb += (int64_t)orr.cout * orr.cin * 2 + orr.cout * 4;
           ab += px * orr.cout * 2;
         }
+      }
+      if ((size_t)i < e->conv_pool.size() && e->conv_pool[i].valid) {
+        // fused with the max-pool behind it: the convolution's own output never reaches HBM, the pooled rows do
+        const dml::Tensor& tp = net.tensors[net.ops[i + 1].out];
+        ab = in_b + (int64_t)tp.h * tp.w * tp.c * e->act_bytes;
       }
       if (e->use_tc && (size_t)i < e->tc.duos.size() && e->tc.duos[i].valid) {
         // fused duo: this launch also does the next block's reduce; the re-read of `out` never reaches HBM
@@ -871,6 +989,22 @@ int dml_duo_bf16(const void* d_y2, const void* d_we, const float* d_be, const vo
   dml::DuoPlan plan;
   if (dml::duo_plan(&plan, a, m) != 0) return fail(DML_EINVAL, "%s", dml::tc_last_error());
   if (dml::launch_duo(plan, a, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
+  return 0;
+}
+
+int dml_conv_pool_bf16(const void* d_in, const void* d_w, const float* d_bias, void* d_pool_out, int n, int hi, int wi, int cin,
+                       int cin_pad, int kh, int kw, int pad, int relu, int pool_pad, void* stream) {
+  if (n < 1) return fail(DML_EINVAL, "n must be positive");
+  if (dml::tc_init() != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
+  dml::ConvParams p{};
+  p.in = d_in; p.w = d_w; p.bias = d_bias; p.res = nullptr; p.out = d_pool_out;  // (the convolution's own output is never written)
+  p.n = n; p.hi = hi; p.wi = wi; p.cin = cin; p.in_pitch = cin;
+  p.ho = hi + 2 * pad - kh + 1; p.wo = wi + 2 * pad - kw + 1;
+  p.cout = 64; p.out_pitch = 64; p.kh = kh; p.kw = kw; p.stride = 1; p.pad_h = pad; p.pad_w = pad; p.cin_pad = cin_pad; p.relu = relu;
+  const int hp = (p.ho + 2 * pool_pad - 3) / 2 + 1, wq = (p.wo + 2 * pool_pad - 3) / 2 + 1;
+  dml::ConvPoolPlan plan;
+  if (dml::conv_pool_plan(&plan, p, hp, wq, pool_pad, n) != 0) return fail(DML_EINVAL, "%s", dml::tc_last_error());
+  if (dml::launch_conv_pool(plan, p, d_pool_out, 64, 0, (cudaStream_t)stream) != 0) return fail(DML_ECUDA, "%s", dml::tc_last_error());
   return 0;
 }
 

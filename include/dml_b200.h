@@ -222,6 +222,15 @@ int dml_duo_bf16(const void* d_y2, const void* d_we, const float* d_be, const vo
                  const void* d_wr, const float* d_br, void* d_y1n, int n, int h, int w, int kmid, int k2, int s2_stride, int nexp,
                  int nred, void* stream);
 
+/* A stride-1 Conv2D with 64 filters (+ folded bias, + ReLU) and the MaxPooling2D(3, strides 2) behind it of predict
+ * (models.py:40 InceptionV3 conv2d_2 + max_pooling2d; models.py:65 ResNet50 conv1 + pool1_pad + pool1_pool) as ONE kernel over
+ * explicit device buffers: bf16 NHWC input [n][hi][wi][cin] (cin 32 with 3 x 3 taps; the engine also runs the 4 x 4 form of
+ * ResNet50's stem over its space-to-depth input), packed bf16 weights [64][kh*kw][cin_pad], fp32 bias; output
+ * [n][hp][wq][64] with hp = (ho + 2 * pool_pad - 3) / 2 + 1.  pool_pad 1 = ZeroPadding2D(1) in front of the pool (needs relu).
+ * Results are bit-identical to dml_conv2d_bf16 followed by the max-pool.  The unit-test hook of that kernel. */
+int dml_conv_pool_bf16(const void* d_in, const void* d_w, const float* d_bias, void* d_pool_out, int n, int hi, int wi, int cin,
+                       int cin_pad, int kh, int kw, int pad, int relu, int pool_pad, void* stream);
+
 /* The dense(1000) + softmax + top-5 head with NO device allocation anywhere: no
  * engine, no workspace.  (No counterpart in the reference: its Keras model owns
  * all of its memory.)  It is for callers that cannot allocate device memory --
