@@ -11,5 +11,5 @@ for MODEL in ResNet50 InceptionV3; do
   echo "launch list $MODEL: ncu exit $?"; wc -l gpurun_out/ncu/launches_$MODEL.csv
 done
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-second-model --sustain-seconds 0 --ncu-step"
-ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:"conv_duo|conv_chain|preprocess_s2d|gap_kernel|fc_tf32|softmax_top5|maxpool3" -c 12 -o gpurun_out/ncu/prof_r02_small $CMD > gpurun_out/ncu/ncu_full.log 2>&1
+ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:"conv_tc6p|conv_duo|conv_chain|preprocess_s2d|gap_kernel|fc_tf32|softmax_top5" -c 14 -o gpurun_out/ncu/prof_r02_small $CMD > gpurun_out/ncu/ncu_full.log 2>&1
 echo "full capture: ncu exit $?"; ls -la gpurun_out/ncu/*.ncu-rep

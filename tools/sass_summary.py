@@ -20,7 +20,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "distributed-machine-learning_b200", "libdml_b200.so")
 KEYS = ["UTCHMMA", "UTCQMMA", "UTCBAR", "UTCATOMSWS", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTMAPF", "UBLKCP", "SYNCS", "HMMA",
         "LDGSTS", "FADD2", "HMNMX2", "ELECT", "ACQBULK", "LDG", "STG", "LDS", "STS"]
-ENGINE_PATH = ["conv_tc2x_kernel", "conv_tc2_kernel", "conv_tc5_kernel", "conv_tc6_kernel", "conv_tc6x_kernel", "conv_chain_kernel", "conv_duo_kernel",
+ENGINE_PATH = ["conv_tc2x_kernel", "conv_tc2_kernel", "conv_tc5_kernel", "conv_tc6_kernel", "conv_tc6x_kernel", "conv_chain_kernel", "conv_duo_kernel", "conv_tc6p_kernel",
                "preprocess_s2d_kernel", "maxpool3_bf16_kernel", "avgpool3_kernel", "gap_kernel", "fc_tf32_kernel", "softmax_top5_kernel"]
 
 
