@@ -3140,16 +3140,17 @@ int conv_pool_plan(ConvPoolPlan* out, const ConvParams& p, int hp, int wq, int p
   const int taps = p.kh * p.kw;
   const size_t b_bytes = ((size_t)taps * c.cpb * V6P_BN * c.row_bytes + 1023) / 1024 * 1024;
   pl.hp = hp; pl.wq = wq; pl.pool_pad = pool_pad; pl.a_stages = 2;
-  // pooled rows per band: the most useful rows per issued MMA row among the band buffers that fit beside two halo stages
+  // pooled rows per band: the most useful rows per issued MMA row among the band buffers that fit beside two halo stages.  A band
+  // that continues its predecessor (most do: a CTA walks consecutive bands) computes 2R rows in T = ceil(2R * Wp / 128) tiles.
   double best = 0;
   for (int R = 1; R <= 16 && R <= hp; ++R) {
     const size_t band = (size_t)(2 * R + 1) * p.wo * 128;
     const size_t smem = 1024 + b_bytes + (size_t)pl.a_stages * c.a_stage_bytes + band + V6P_BN * 4 + 16 + 256;
-    if (smem > (size_t)SMEM_LIMIT || (2 * R + 1) * c.wp + BLOCK_M >= 65536) break;
-    const int T = ((2 * R + 1) * c.wp + BLOCK_M - 1) / BLOCK_M;
-    const int bands = (hp + R - 1) / R;
-    const double eff = (double)hp * 2 * p.wo / ((double)bands * T * BLOCK_M);  // new convolution rows per issued MMA row
-    if (eff > best) { best = eff; pl.R = R; pl.T = T; pl.bands = bands; pl.smem = smem; }
+    if (smem > (size_t)SMEM_LIMIT || (2 * R + 2) * c.wp + BLOCK_M >= 65536) break;
+    const int T = (2 * R * c.wp + BLOCK_M - 1) / BLOCK_M;
+    // new convolution rows per issued MMA row; half a tile per band for its pooling pass, row move and barriers
+    const double eff = (double)2 * R * p.wo / (((double)T + 0.5) * BLOCK_M);
+    if (eff >= best) { best = eff; pl.R = R; pl.T = T; pl.bands = (hp + R - 1) / R; pl.smem = smem; }
   }
   if (pl.R == 0) return tc_fail("conv + pool kernel: no band of pooled rows fits in shared memory (row of %d pixels)", p.wo);
   pl.valid = true;
@@ -3168,7 +3169,7 @@ int launch_conv_pool(const ConvPoolPlan& pl, const ConvParams& p, void* pool_out
   k.n_img = p.n; k.ho = p.ho; k.wo = p.wo; k.wp = c.wp;
   k.hp = pl.hp; k.wq = pl.wq; k.out_pitch = pool_out_pitch; k.pool_pad = pl.pool_pad;
   k.pad_h = p.pad_h; k.pad_w = p.in_row_cells ? 0 : p.pad_w;
-  k.R = pl.R; k.bands = pl.bands; k.T = pl.T;
+  k.R = pl.R; k.bands = pl.bands;
   k.rows_box = c.rows_box; k.a_cb_bytes = c.a_cb_bytes; k.a_stage_bytes = c.a_stage_bytes; k.a_stages = pl.a_stages;
   k.relu = p.relu; k.tmem_cols = 4 * V6P_BN;
   k.in_img0 = p.in_img0; k.out_img0 = pool_out_img0;
