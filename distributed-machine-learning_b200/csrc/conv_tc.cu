@@ -2037,6 +2037,7 @@ PFN_cuTensorMapEncodeIm2col g_encode_im2col = nullptr;
 int g_driver_version = 0;
 
 int g_num_sms = 148;
+int g_smem_aligned = -1;  // 1: dynamic shared memory starts at a multiple of 1024 bytes (probed in tc_init)
 
 int pick_bn(int cout, int override_bn) {
   if (override_bn > 0) return (cout % override_bn == 0 && override_bn % 16 == 0 && override_bn <= 256) ? override_bn : 0;
@@ -2131,6 +2132,12 @@ int tc_init() {
   int dev = 0, sms = 0;
   if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0)
     g_num_sms = sms;
+  if (g_smem_aligned < 0) {  // does dynamic shared memory start 1 KiB-aligned?  (duo_plan: the conv3_block1 shape fits only without slack)
+    int mod = -1;
+    smem_base_probe_kernel<<<1, 32, 2048>>>();
+    if (cudaMemcpyFromSymbol(&mod, g_smem_base_mod, sizeof mod) == cudaSuccess) g_smem_aligned = mod == 0 ? 1 : 0;
+    else (void)cudaGetLastError();
+  }
   return 0;
 }
 
@@ -3000,7 +3007,7 @@ int duo_plan(DuoPlan* out, const DuoArgs& a, int m_capacity) {
   const int opts[9][4] = {{8, 2, 2, 2}, {8, 1, 3, 3}, {8, 1, 2, 2}, {4, 2, 4, 4}, {4, 2, 3, 2}, {4, 2, 2, 2}, {4, 1, 4, 3}, {4, 1, 3, 2}, {4, 1, 2, 2}};
   static const int slots_env = getenv("DML_DUO_SLOTS") ? atoi(getenv("DML_DUO_SLOTS")) : 8;  // experiments: 4 = never more than four slots
   bool fit = false;
-  for (int pass = 0; pass < 2 && !fit; ++pass)  // second pass: without the 1 KiB of slack for aligning the base (conv3_block1: exactly 227 KiB)
+  for (int pass = 0; pass < (g_smem_aligned == 1 ? 2 : 1) && !fit; ++pass)  // second pass: without the 1 KiB of slack for aligning the base (conv3_block1: exactly 227 KiB)
     for (const auto& o : opts) {
       if (o[0] > slots_env) continue;
       const DuoSmem L = duo_smem(kmb, nj, a.nred, o[1], o[2], o[3], o[0]);
